@@ -1,0 +1,193 @@
+/* snb.h — C ABI of synerfgine_b200 (libsnb.so): the SyNeRFgine render hot path on B200 (sm_100a).
+ *
+ * Drop-in boundary. Each entry point names the reference interface it replaces; paths are
+ * relative to the reference checkout (trxe/SyNeRFgine @ b842828).
+ *
+ * Conventions: every function returns 0 on success and a negative snb_status otherwise; the message is
+ * available from snb_last_error(). No exceptions cross this boundary. Pointers named *_dev are CUDA device
+ * pointers on the context's device, *_host are host pointers; nothing else is dereferenced. All work is
+ * enqueued on the context's stream; calls that hand results to the host synchronise that stream, all others
+ * are asynchronous until snb_sync(). One context per host thread. There is no CPU fallback: without a CUDA
+ * device snb_create fails.
+ */
+#ifndef SNB_H
+#define SNB_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct snb_ctx snb_ctx;
+
+enum snb_status { SNB_OK = 0, SNB_ERR_ARG = -1, SNB_ERR_CUDA = -2, SNB_ERR_STATE = -3, SNB_ERR_IO = -4, SNB_ERR_PARSE = -5, SNB_ERR_UNSUPPORTED = -6 };
+
+/* ENerfActivation, include/neural-graphics-primitives/common.h */
+enum { SNB_ACT_NONE = 0, SNB_ACT_RELU = 1, SNB_ACT_LOGISTIC = 2, SNB_ACT_EXPONENTIAL = 3 };
+/* ERenderMode, include/neural-graphics-primitives/common.h:56-68 */
+enum { SNB_MODE_AO = 0, SNB_MODE_SHADE = 1, SNB_MODE_NORMALS = 2, SNB_MODE_POSITIONS = 3, SNB_MODE_DEPTH = 4, SNB_MODE_SHADOWDEPTH = 8 };
+/* ETonemapCurve */
+enum { SNB_TONEMAP_IDENTITY = 0, SNB_TONEMAP_ACES = 1, SNB_TONEMAP_HABLE = 2, SNB_TONEMAP_REINHARD = 3 };
+/* sng::ImgBufferType, include/synerfgine/raytracer.cuh:20-31 */
+enum { SNB_BUF_FINAL = 0, SNB_BUF_NEXT_ORIGIN = 1, SNB_BUF_SRC_ORIGIN = 2, SNB_BUF_NEXT_DIRECTION = 3, SNB_BUF_SRC_DIRECTION = 4,
+       SNB_BUF_NORMAL = 5, SNB_BUF_DEPTH = 6, SNB_BUF_NERF_SHADOW = 7 };
+
+/* A NeRF model: what Testbed holds after load_snapshot (src/testbed.cu:4878-4992) — NerfNetwork parameters
+ * (include/neural-graphics-primitives/nerf_network.h:356-371 order: density MLP, rgb MLP, hash grid; fp16),
+ * the occupancy bitfield (src/testbed_nerf.cu:3212-3229), boxes and activations. Host pointers; copied. */
+typedef struct {
+	uint32_t n_levels, n_features_per_level, log2_hashmap_size, base_resolution;
+	float per_level_scale;
+	const uint16_t* params;      /* fp16 bits */
+	uint64_t n_params;
+	const uint8_t* bitfield;     /* 8 * 128^3 / 8 bytes, Morton order; NULL = occupied everywhere */
+	float aabb_min[3], aabb_max[3];
+	float render_aabb_min[3], render_aabb_max[3];
+	float render_aabb_to_local[9];   /* column-major mat3 */
+	uint32_t max_cascade;
+	float cone_angle_constant;
+	int32_t rgb_activation, density_activation;
+	float min_transmittance;
+} snb_model_desc;
+
+/* Camera + image of one render call: CudaRenderBufferView (render_buffer.h:169-178) + the camera arguments
+ * of render_nerf (testbed.h:358-371). */
+typedef struct {
+	float camera[12];            /* mat4x3, column-major */
+	float focal_length[2];       /* pixels: calc_focal_length (src/testbed.cu:4133-4135) */
+	float screen_center[2];
+	int32_t width, height;
+	uint32_t spp;                /* sample index of the accumulation */
+	int32_t snap_to_pixel_centers;
+} snb_view;
+
+/* Pixel tile of a view rendered by this context (multi-GPU sharding). Pixel indices used for
+ * sampling stay global. A zero-sized tile means the whole view. */
+typedef struct { int32_t x0, y0, w, h; } snb_tile;
+
+typedef struct {                 /* sng::ObjectTransform (include/synerfgine/common.cuh:137-147), host arrays */
+	const float* nodes;          /* n_nodes * 8 floats: bb.min, bb.max, left_idx, right_idx (ints) */
+	const float* tris;           /* n_tris * 9 floats */
+	int32_t n_nodes, n_tris;
+	float rot[9];                /* column-major */
+	float pos[3];
+	float scale;
+	int32_t mat_id;
+} snb_object;
+
+typedef struct {                 /* sng::Material (include/synerfgine/material.cuh:125-134) */
+	float ka[3], kd[3], ks[3];
+	float n, rg;
+	int32_t type;                /* 0 lambertian, 1 glossy */
+	float spec_angle;
+} snb_material;
+
+typedef struct {                 /* sng::Light (include/synerfgine/light.cuh:79-91) */
+	float pos[3];
+	int32_t type;                /* 0 point, 1 directional */
+	float intensity, size;
+} snb_light;
+
+/* RayTracer members (raytracer.cuh:156-167) + Engine shadow settings (engine.cuh:112-120) = "rendering" JSON. */
+typedef struct {
+	uint32_t n_steps;            /* shadow DDA steps (8) */
+	uint32_t samples;            /* light_samples */
+	uint32_t bounces;            /* path_trace_depth */
+	uint32_t shadow_iters;       /* syn_shadow_samples */
+	float lens_angle_constant;   /* lens_size */
+	float depth_offset;
+	float syn_shadow_factor;     /* syn_shadow_intensity */
+	int32_t view_nerf_shadow;    /* shadow_on_virtual_obj */
+	int32_t buffer_type;
+	int32_t nerf_shadow_kernel;  /* nerf_shadow_samples */
+	float nerf_shadow_intensity;
+	float nerf_on_nerf_shadow_threshold;
+	int32_t show_shadow_on_nerf; /* shadow_on_nerf */
+	int32_t show_nerf;
+	int32_t syn_px_scale;
+	float exposure;
+	int32_t tonemap_curve;
+} snb_rt_params;
+
+/* ---- lifetime ----------------------------------------------------------------------------------------- */
+int snb_create(int device, void* cuda_stream /* cudaStream_t or NULL */, snb_ctx** out);
+void snb_destroy(snb_ctx* ctx);
+const char* snb_last_error(const snb_ctx* ctx);
+int snb_sync(snb_ctx* ctx);
+const char* snb_version(void);
+
+/* ---- inputs ------------------------------------------------------------------------------------------- */
+/* ≙ Testbed::load_snapshot result handed over as arrays (src/testbed.cu:4878-4992). */
+int snb_set_model(snb_ctx* ctx, const snb_model_desc* model);
+/* ≙ Engine::set_virtual_world after parsing (src/synerfgine/engine.cu:21-78): uploads world, materials, lights. */
+int snb_set_scene(snb_ctx* ctx, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
+                  const snb_light* lights, uint32_t n_lights);
+/* ≙ Engine::update_world_objects (engine.cu:80-127): per-frame transforms / lights without re-uploading meshes. */
+int snb_update_scene(snb_ctx* ctx, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
+                     const snb_light* lights, uint32_t n_lights);
+/* ≙ sng::init_rand_state (src/synerfgine/common.cu:22-26) for both state arrays; seed 1999 in the reference. */
+int snb_seed_rng(snb_ctx* ctx, uint64_t seed);
+/* Clears the ray tracer's temporal blend buffer (≙ RayTracer::m_reset_color_buffer, raytracer.cu:327-336). */
+int snb_reset_accumulation(snb_ctx* ctx);
+
+/* ---- the hot path ------------------------------------------------------------------------------------- */
+/* ≙ Testbed::render_nerf (testbed.h:358-371; src/testbed_nerf.cu:2679-2837): stock NeRF frame into fb/depth. */
+int snb_render_nerf(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, int render_mode, float* fb_rgba_dev, float* depth_dev);
+/* ≙ RayTracer::render (raytracer.cuh:116-128; src/synerfgine/raytracer.cu:312-370): mesh layer into the
+ * context's syn buffers; optional copies out. */
+int snb_render_syn(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* syn_rgba_dev, float* syn_depth_dev);
+/* ≙ Testbed::render sng overload → render_nerf_with_buffers + shade_nerf_shadows (testbed.h:323-357,401-418;
+ * src/testbed.cu:4353-4404; src/testbed_nerf.cu:2467-2677). positions/normals may be NULL (context scratch). */
+int snb_render_nerf_with_buffers(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, int render_mode,
+                                 float* fb_rgba_dev, float* depth_dev, float* positions_dev, float* normals_dev);
+/* ≙ RayTracer::overlay (raytracer.cuh:130-131; raytracer.cu:372-392). */
+int snb_overlay(snb_ctx* ctx, int syn_w, int syn_h, const snb_rt_params* rt, const float* syn_rgba_dev, const float* syn_depth_dev,
+                const float* nerf_rgba_dev, const float* nerf_depth_dev, float* out_rgba_dev, float* out_depth_dev);
+/* ≙ render_frame_epilogue → CudaRenderBuffer::accumulate + tonemap (src/testbed.cu:4550-4627; render_buffer.cu:671-735). */
+int snb_accumulate_tonemap(snb_ctx* ctx, int n_pixels, const float* frame_rgba_dev, float* accumulate_rgba_dev, uint32_t spp, int color_space_srgb,
+                           int output_srgb, float exposure, const float* background_rgba4, int tonemap_curve, float* out_rgba_dev);
+/* ≙ Engine::frame minus GL (src/synerfgine/engine.cu:352-433): syn layer, NeRF layer with both shadow
+ * directions, overlay. Output on the device … */
+int snb_frame(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_dev, float* out_depth_dev);
+/* … or copied into host buffers (tile-sized; what a host-language caller over cgo/JNI/ctypes uses). */
+int snb_frame_host(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_host, float* out_depth_host);
+
+/* ---- parity taps (the reference's debug views: positions, depth, hit indices — SURVEY.md §4) -------------- */
+/* Per-ray march sample sequence: t, dt, cell = mip << 24 | morton (0xFFFFFFFF padding), n per ray. */
+int snb_march_trace(snb_ctx* ctx, const snb_view* view, uint32_t max_samples, float* t_dev, float* dt_dev, uint32_t* cell_dev, uint32_t* n_dev,
+                    float* origin_dir_dev /* n x 6 or NULL */);
+/* ≙ NerfNetwork::inference_mixed_precision (nerf_network.h:105-139): coords n x 7 fp32 → n x 4 fp16 (rgb, sigma);
+ * optional features n x 32 fp16 and hash indices n x (n_levels * 8). */
+int snb_network_inference(snb_ctx* ctx, const float* coords_dev, uint64_t n, uint16_t* out_dev, uint16_t* features_dev, uint32_t* hash_idx_dev);
+/* ≙ depth_test_world closest hit (src/synerfgine/common.cu:36-67): rays n x 6 → object id, triangle id, t. */
+int snb_trace_rays(snb_ctx* ctx, const float* rays_dev, uint32_t n, int32_t* obj_id_dev, int32_t* tri_id_dev, float* t_dev);
+/* Counters of the last NeRF render: [0] network samples, [1] rays launched, [2] rays that hit, [3] march batches. */
+int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
+/* Number of kernels this context has launched so far. */
+uint64_t snb_launch_count(const snb_ctx* ctx);
+
+/* ---- host-side scene layer (C++ in the reference: Engine / VirtualObject / CamPath / TriangleBvh::build) ---- */
+typedef struct snb_scene snb_scene;
+/* ≙ Engine::set_virtual_world + Engine::init "rendering" block (engine.cu:21-78,129-234). obj paths resolve against base_dir. */
+int snb_scene_load_json(const char* json_text, const char* base_dir, snb_scene** out, char* err, size_t err_len);
+void snb_scene_free(snb_scene* s);
+int snb_scene_counts(const snb_scene* s, uint32_t* n_objects, uint32_t* n_materials, uint32_t* n_lights);
+int snb_scene_get(const snb_scene* s, snb_object* objects, snb_material* materials, snb_light* lights, snb_rt_params* rt);
+/* camera block: view dir, look-at, zoom, vo_scale + keyframe path; frame index advances CamPath (cam_path.cuh:116-142). */
+int snb_scene_camera(const snb_scene* s, float* view3, float* at3, float* zoom, float* vo_scale, uint32_t* n_keyframes);
+int snb_scene_camera_at(const snb_scene* s, uint32_t frame, uint32_t total_frames, float* view3, float* at3, float* zoom);
+/* ≙ VirtualObject::next_frame / Light::next_frame (virtual_object.cuh:53-64; light.cuh:40-49). */
+int snb_scene_advance(snb_scene* s);
+/* ≙ TriangleBvhWithBranchingFactor<2>::build (src/triangle_bvh.cu:615-718); reorders tris in place. */
+int snb_bvh_build(float* tris, int32_t n_tris, int32_t prims_per_leaf, float* nodes_out, int32_t nodes_cap, int32_t* n_nodes_out);
+/* ≙ tinyobj::LoadObj as used by VirtualObject (src/synerfgine/virtual_object.cu:38-75): triangles n x 9. */
+int snb_obj_load(const char* path, float* tris_out, int32_t tris_cap, int32_t* n_tris_out);
+/* ≙ grid_to_bitfield + bitfield_max_pool (src/testbed_nerf.cu:285-332,3212-3229), device kernels. density: fp32
+ * [(max_cascade+1) * 128^3] Morton-ordered host array; out: 8 * 128^3 / 8 bytes host. */
+int snb_density_to_bitfield(snb_ctx* ctx, const float* density_host, uint32_t max_cascade, uint8_t* bitfield_out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SNB_H */

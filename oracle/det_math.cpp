@@ -8,6 +8,12 @@
 //   det_expf(x): n = floor(fmaf(x, LOG2E, 0.5)), clamped to [-125, 126];
 //       r = fmaf(-n, LN2_HI, x); r = fmaf(-n, LN2_LO, r)
 //       q = 1 + r + r^2/2 + ... + r^8/40320 (Horner with fmaf); result = q * 2^n (exponent-field add)
+//   det_sinf(x), x in [0, pi/2]: odd Taylor polynomial through x^13, Horner with fmaf in z = x*x:
+//       s = x * (1 + z*(-1/6 + z*(1/120 + z*(-1/5040 + z*(1/362880 + z*(-1/39916800 + z/6227020800))))))
+//   det_acosf(c), c in [0, 1]:  asin_small(s) = s * (1 + z*(1/6 + z*(3/40 + z*(15/336 + z*(105/3456
+//       + z*(945/42240 + z*(10395/599040 + z*(135135/9676800 + z*(2027025/175472640))))))))), z = s*s
+//       c > 0.5:  2 * asin_small(sqrt((1 - c) * 0.5));   else:  PI_2 - asin_small(c)
+//       (used only by the camera quaternion slerp, tcnn/vec.h:1121-1142, when its trig branch is taken)
 // They replace logf/expf only inside the exponential stepping functions
 // (nerf_device.cuh:379-431 to_stepping_space / from_stepping_space) when math mode is MATH_DET.
 #include "oracle_common.h"
@@ -60,10 +66,43 @@ float det_expf(float x) {
 	return u2f(f2u(q) + ((uint32_t)n << 23));
 }
 
+float det_sinf(float x) {
+	float z = x * x;
+	float p = 1.0f / 6227020800.0f;
+	p = std::fmaf(p, z, -1.0f / 39916800.0f);
+	p = std::fmaf(p, z, 1.0f / 362880.0f);
+	p = std::fmaf(p, z, -1.0f / 5040.0f);
+	p = std::fmaf(p, z, 1.0f / 120.0f);
+	p = std::fmaf(p, z, -1.0f / 6.0f);
+	p = std::fmaf(p, z, 1.0f);
+	return x * p;
+}
+
+static float det_asin_small(float s) {
+	float z = s * s;
+	float p = 2027025.0f / 175472640.0f;
+	p = std::fmaf(p, z, 135135.0f / 9676800.0f);
+	p = std::fmaf(p, z, 10395.0f / 599040.0f);
+	p = std::fmaf(p, z, 945.0f / 42240.0f);
+	p = std::fmaf(p, z, 105.0f / 3456.0f);
+	p = std::fmaf(p, z, 15.0f / 336.0f);
+	p = std::fmaf(p, z, 3.0f / 40.0f);
+	p = std::fmaf(p, z, 1.0f / 6.0f);
+	p = std::fmaf(p, z, 1.0f);
+	return s * p;
+}
+
+float det_acosf(float c) {
+	if (c > 0.5f) return 2.0f * det_asin_small(std::sqrt((1.0f - c) * 0.5f));
+	return 1.57079632679489662f - det_asin_small(c);
+}
+
 } // namespace orc
 
 extern "C" {
 void orc_set_math_mode(int mode) { orc::g_math_mode = mode; }
 float orc_det_logf(float x) { return orc::det_logf(x); }
 float orc_det_expf(float x) { return orc::det_expf(x); }
+float orc_det_sinf(float x) { return orc::det_sinf(x); }
+float orc_det_acosf(float x) { return orc::det_acosf(x); }
 }

@@ -277,8 +277,8 @@ static quat qslerp(quat x, quat y, float t) {
 	if (cos_theta > 1.0f - std::numeric_limits<float>::epsilon()) {
 		return qadd(qscale(x, 1.0f - t), qscale(z, t));  // mix(), vec.h:1102
 	}
-	float angle = std::acos(cos_theta);
-	return qdiv(qadd(qscale_l(std::sin((1.0f - t) * angle), x), qscale_l(std::sin(t * angle), z)), std::sin(angle));
+	float angle = m_acosf(cos_theta);
+	return qdiv(qadd(qscale_l(m_sinf((1.0f - t) * angle), x), qscale_l(m_sinf(t * angle), z)), m_sinf(angle));
 }
 // vec.h:1099-1110: note length2() already takes a sqrt, so "length" is the 4th root of dot(a,a).
 static quat qnormalize(quat a) {

@@ -29,6 +29,10 @@ enum MathMode { MATH_LIBM = 0, MATH_DET = 1 };
 extern int g_math_mode;
 float det_logf(float x);
 float det_expf(float x);
+float det_sinf(float x);
+float det_acosf(float x);
+inline float m_sinf(float x) { return g_math_mode == MATH_DET ? det_sinf(x) : std::sin(x); }
+inline float m_acosf(float x) { return g_math_mode == MATH_DET ? det_acosf(x) : std::acos(x); }
 inline float m_logf(float x) { return g_math_mode == MATH_DET ? det_logf(x) : std::log(x); }
 inline float m_expf(float x) { return g_math_mode == MATH_DET ? det_expf(x) : std::exp(x); }
 

@@ -1,0 +1,205 @@
+// synerfgine_b200 — C ABI implementation (include/snb.h): lifetime, inputs, the render entry points and taps.
+// Host orchestration follows Engine::frame (reference src/synerfgine/engine.cu:352-433), Testbed::render sng
+// overload (src/testbed.cu:4353-4404), render_nerf_with_buffers / shade_nerf_shadows / render_nerf
+// (src/testbed_nerf.cu:2467-2837) and RayTracer::render / overlay (src/synerfgine/raytracer.cu:312-392) — minus
+// every host<->device sync inside the frame: the march loop is device-resident, so a frame is a fixed sequence of
+// launches on one stream.
+#include <cstring>
+#include <cmath>
+#include <algorithm>
+#include "snb_context.cuh"
+
+using namespace snb;
+
+static v3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+static m3 ldm3(const float* p) { m3 m; m.c0 = ld3(p); m.c1 = ld3(p + 3); m.c2 = ld3(p + 6); return m; }
+
+// tcnn grid_scale / grid_resolution (common_device.h:841-850) and the level offset table (encodings/grid.h:692-723).
+static GridDesc make_grid_desc(uint32_t n_levels, uint32_t F, uint32_t log2_T, uint32_t base_res, float per_level_scale) {
+	GridDesc g; memset(&g, 0, sizeof g);
+	g.n_levels = n_levels; g.n_feat = F;
+	const float log2_pls = std::log2(per_level_scale);
+	uint32_t offset = 0;
+	for (uint32_t i = 0; i < n_levels; ++i) {
+		const float scale = std::exp2(i * log2_pls) * base_res - 1.0f;
+		const uint32_t res = (uint32_t)std::ceil(scale) + 1;
+		const uint32_t max_params = 0xFFFFFFFFu / 2;
+		uint32_t n = std::pow((float)res, 3) > (float)max_params ? max_params : res * res * res;
+		n = (n + 7u) / 8u * 8u;
+		n = std::min(n, 1u << log2_T);
+		g.scale[i] = scale; g.res[i] = res; g.offset[i] = offset;
+		offset += n;
+	}
+	g.offset[n_levels] = offset;
+	return g;
+}
+
+extern "C" {
+
+const char* snb_version(void) { return "synerfgine_b200 0.1 (sm_100a)"; }
+
+int snb_create(int device, void* cuda_stream, snb_ctx** out) {
+	if (!out) return SNB_ERR_ARG;
+	*out = nullptr;
+	int n_dev = 0;
+	if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) return SNB_ERR_CUDA;   // no CPU fallback
+	if (device < 0 || device >= n_dev) return SNB_ERR_ARG;
+	if (cudaSetDevice(device) != cudaSuccess) return SNB_ERR_CUDA;
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return SNB_ERR_CUDA;
+	if (prop.major < 10) return SNB_ERR_UNSUPPORTED;   // sm_100a binary only
+	snb_ctx* c = new snb_ctx();
+	c->device = device;
+	c->sm_count = prop.multiProcessorCount;
+	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
+	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
+	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
+	cudaMemsetAsync(c->d_counters.p, 0, sizeof(NerfCounters), c->stream);
+	memset(&c->model, 0, sizeof c->model);
+	*out = c;
+	return SNB_OK;
+}
+
+void snb_destroy(snb_ctx* c) {
+	if (!c) return;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
+	                  &c->d_counters, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
+	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
+	for (DevBuf* b : bufs) b->release();
+	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	if (c->own_stream) cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+const char* snb_last_error(const snb_ctx* c) { return c ? c->err.c_str() : "null context"; }
+uint64_t snb_launch_count(const snb_ctx* c) { return c ? c->launches : 0; }
+
+int snb_sync(snb_ctx* c) {
+	if (!c) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	return SNB_OK;
+}
+
+int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
+	if (!c || !m || !m->params) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const uint32_t F = m->n_features_per_level, L = m->n_levels;
+	if (!(F == 1 || F == 2 || F == 4 || F == 8) || L * F != (uint32_t)kFeat || L > (uint32_t)kMaxLevels)
+		return c->fail(SNB_ERR_UNSUPPORTED, "encoding must satisfy n_levels * n_features_per_level == 32 with F in {1,2,4,8}");
+	if (m->max_cascade >= kCascades) return c->fail(SNB_ERR_ARG, "max_cascade must be < 8");
+	GridDesc g = make_grid_desc(L, F, m->log2_hashmap_size, m->base_resolution, m->per_level_scale);
+	const uint64_t n_grid = (uint64_t)g.offset[L] * F;
+	if (m->n_params != (uint64_t)kMlpHalves + n_grid) return c->fail(SNB_ERR_ARG, "n_params does not match the network architecture");
+	SNB_CUDA(c, c->d_mlp.reserve(kMlpHalves * 2));
+	SNB_CUDA(c, c->d_mlp_frag.reserve(kFragWords * 4));
+	SNB_CUDA(c, c->d_grid.reserve(n_grid * 2));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp.p, m->params, kMlpHalves * 2, cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_grid.p, m->params + kMlpHalves, n_grid * 2, cudaMemcpyHostToDevice, c->stream));
+	std::vector<uint32_t> frag(kFragWords);
+	build_mma_fragments(m->params, frag.data());
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp_frag.p, frag.data(), kFragWords * 4, cudaMemcpyHostToDevice, c->stream));
+	const size_t bf_bytes = (size_t)kCascades * kGridCells / 8;
+	if (m->bitfield) {
+		SNB_CUDA(c, c->d_bitfield.reserve(bf_bytes));
+		SNB_CUDA(c, cudaMemcpyAsync(c->d_bitfield.p, m->bitfield, bf_bytes, cudaMemcpyHostToDevice, c->stream));
+	}
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // host staging vectors go out of scope
+
+	DevModel& d = c->model;
+	d.grid = g;
+	d.grid_params = c->d_grid.as<__half>();
+	d.mlp_rowmajor = c->d_mlp.as<__half>();
+	d.mlp_frag = c->d_mlp_frag.as<uint32_t>();
+	d.mlp_umma = nullptr;
+	d.train_aabb.lo = ld3(m->aabb_min); d.train_aabb.hi = ld3(m->aabb_max);
+	d.rgb_act = m->rgb_activation; d.density_act = m->density_activation;
+	d.min_transmittance = m->min_transmittance;
+	d.env.bitfield = m->bitfield ? c->d_bitfield.as<uint8_t>() : nullptr;
+	d.env.min_mip = 0; d.env.max_mip = m->max_cascade;
+	d.env.render_aabb.lo = ld3(m->render_aabb_min); d.env.render_aabb.hi = ld3(m->render_aabb_max);
+	d.env.to_local = ldm3(m->render_aabb_to_local);
+	d.env.st = make_stepping(m->cone_angle_constant);
+	c->feat_per_level = F;
+	c->has_model = true;
+	return SNB_OK;
+}
+
+static int upload_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
+                             const snb_light* lights, uint32_t n_lights) {
+	std::vector<DevObject> ho(n_objects);
+	for (uint32_t i = 0; i < n_objects; ++i) {
+		DevObject& o = ho[i];
+		o.nodes = c->obj_store[i].nodes.as<float>(); o.tris = c->obj_store[i].tris.as<float>();
+		o.n_nodes = c->obj_store[i].n_nodes; o.n_tris = c->obj_store[i].n_tris;
+		o.rot = ldm3(objects[i].rot);
+		o.inv_sr = mul(identity3() / objects[i].scale, inverse(o.rot));   // ngp::ray_intersect_nodes, src/triangle_bvh.cu:313-319
+		o.pos = ld3(objects[i].pos); o.scale = objects[i].scale; o.mat_id = objects[i].mat_id;
+	}
+	std::vector<DevMaterial> hm(n_materials);
+	for (uint32_t i = 0; i < n_materials; ++i) {
+		hm[i].ka = ld3(materials[i].ka); hm[i].kd = ld3(materials[i].kd); hm[i].ks = ld3(materials[i].ks);
+		hm[i].n = materials[i].n; hm[i].rg = materials[i].rg; hm[i].type = materials[i].type; hm[i].spec_angle = materials[i].spec_angle;
+	}
+	std::vector<DevLight> hl(n_lights);
+	for (uint32_t i = 0; i < n_lights; ++i) { hl[i].pos = ld3(lights[i].pos); hl[i].type = lights[i].type; hl[i].intensity = lights[i].intensity; hl[i].size = lights[i].size; }
+	SNB_CUDA(c, c->d_objects.reserve(std::max<size_t>(1, n_objects) * sizeof(DevObject)));
+	SNB_CUDA(c, c->d_materials.reserve(std::max<size_t>(1, n_materials) * sizeof(DevMaterial)));
+	SNB_CUDA(c, c->d_lights.reserve(std::max<size_t>(1, n_lights) * sizeof(DevLight)));
+	if (n_objects) SNB_CUDA(c, cudaMemcpyAsync(c->d_objects.p, ho.data(), n_objects * sizeof(DevObject), cudaMemcpyHostToDevice, c->stream));
+	if (n_materials) SNB_CUDA(c, cudaMemcpyAsync(c->d_materials.p, hm.data(), n_materials * sizeof(DevMaterial), cudaMemcpyHostToDevice, c->stream));
+	if (n_lights) SNB_CUDA(c, cudaMemcpyAsync(c->d_lights.p, hl.data(), n_lights * sizeof(DevLight), cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	c->scene.objects = c->d_objects.as<DevObject>(); c->scene.n_objects = n_objects;
+	c->scene.materials = c->d_materials.as<DevMaterial>(); c->scene.n_materials = n_materials;
+	c->scene.lights = c->d_lights.as<DevLight>(); c->scene.n_lights = n_lights;
+	c->syn_reset = true;   // anything moved -> accumulation restarts (engine.cu:80-127)
+	return SNB_OK;
+}
+
+int snb_set_scene(snb_ctx* c, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
+                  const snb_light* lights, uint32_t n_lights) {
+	if (!c || (n_objects && !objects) || (n_materials && !materials) || (n_lights && !lights)) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	for (uint32_t i = 0; i < n_objects; ++i) {
+		if (!objects[i].nodes || !objects[i].tris || objects[i].n_nodes <= 0 || objects[i].n_tris <= 0) return c->fail(SNB_ERR_ARG, "object without BVH nodes or triangles");
+		if (objects[i].mat_id < 0 || (uint32_t)objects[i].mat_id >= n_materials) return c->fail(SNB_ERR_ARG, "object material index out of range");
+	}
+	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	c->obj_store.assign(n_objects, ObjectStore());
+	for (uint32_t i = 0; i < n_objects; ++i) {
+		ObjectStore& s = c->obj_store[i];
+		s.n_nodes = objects[i].n_nodes; s.n_tris = objects[i].n_tris;
+		SNB_CUDA(c, s.nodes.reserve((size_t)s.n_nodes * 32));
+		SNB_CUDA(c, s.tris.reserve((size_t)s.n_tris * 36));
+		SNB_CUDA(c, cudaMemcpyAsync(s.nodes.p, objects[i].nodes, (size_t)s.n_nodes * 32, cudaMemcpyHostToDevice, c->stream));
+		SNB_CUDA(c, cudaMemcpyAsync(s.tris.p, objects[i].tris, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+	}
+	return upload_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights);
+}
+
+int snb_update_scene(snb_ctx* c, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
+                     const snb_light* lights, uint32_t n_lights) {
+	if (!c) return SNB_ERR_ARG;
+	if (n_objects != c->obj_store.size()) return c->fail(SNB_ERR_STATE, "snb_update_scene: object count differs from snb_set_scene");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	return upload_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights);
+}
+
+int snb_seed_rng(snb_ctx* c, uint64_t seed) {
+	if (!c) return SNB_ERR_ARG;
+	c->rng_seed = seed; c->rng_dirty = true;
+	return SNB_OK;
+}
+
+int snb_reset_accumulation(snb_ctx* c) {
+	if (!c) return SNB_ERR_ARG;
+	c->syn_reset = true;
+	return SNB_OK;
+}
+
+} // extern "C"
+
+#include "snb_render.inl"
+#include "snb_taps.inl"

@@ -1,0 +1,76 @@
+// synerfgine_b200 — host-side context behind the C ABI: owns the device copies of the model and the scene, the
+// persistent scratch (ray queue, RNG states, layer buffers) and the stream all kernels are enqueued on.
+// Mirrors the state the reference spreads over Testbed (network, bitfield, render buffers), sng::Engine
+// (world / material / light arrays, NeRF RNG states, normals, positions) and sng::RayTracer (ray SoA, RNG
+// states, temporal accumulation) — include/synerfgine/engine.cuh:79-120, raytracer.cuh:150-182.
+#pragma once
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "../../include/snb.h"
+#include "snb_device.cuh"
+#include "snb_nerf_kernels.cuh"
+#include "snb_sng_kernels.cuh"
+
+namespace snb {
+
+// Grow-only device buffer (the reference re-acquires arena scratch every frame, src/testbed_nerf.cu:2403-2435).
+struct DevBuf {
+	void* p = nullptr; size_t cap = 0;
+	cudaError_t reserve(size_t bytes) {
+		if (bytes <= cap) return cudaSuccess;
+		if (p) cudaFree(p);
+		p = nullptr; cap = 0;
+		cudaError_t e = cudaMalloc(&p, bytes);
+		if (e == cudaSuccess) cap = bytes;
+		return e;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+	template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct ObjectStore { DevBuf nodes, tris; int n_nodes = 0, n_tris = 0; };
+
+} // namespace snb
+
+struct snb_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	bool own_stream = false;
+	std::string err;
+	int sm_count = 148;
+	uint64_t launches = 0;
+
+	// model
+	bool has_model = false;
+	snb::DevModel model;
+	uint32_t feat_per_level = 2;
+	snb::DevBuf d_grid, d_mlp, d_mlp_frag, d_mlp_umma, d_bitfield;
+
+	// scene
+	std::vector<snb::ObjectStore> obj_store;
+	snb::DevBuf d_objects, d_materials, d_lights;
+	snb::DevScene scene{nullptr, 0, nullptr, 0, nullptr, 0};
+
+	// scratch
+	snb::DevBuf d_queue, d_qctl, d_counters;
+	snb::DevBuf d_rng_nerf, d_rng_syn;
+	int rng_w = 0, rng_h = 0, rng_tx0 = -1, rng_ty0 = -1, rng_tw = 0, rng_th = 0, rng_scale = 0;
+	uint64_t rng_seed = 1999;          // PT_SEED, include/synerfgine/common.cuh:20
+	bool rng_dirty = true;
+	snb::DevBuf d_syn_origins, d_syn_dirs, d_syn_rgba, d_syn_depth;
+	bool syn_reset = true;
+	int syn_w = 0, syn_h = 0;
+	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
+	int fused_blocks_per_sm = 0;
+
+	int fail(int code, const std::string& msg) { err = msg; return code; }
+	int cuda_fail(cudaError_t e, const char* what) {
+		char buf[256]; snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+		err = buf; return SNB_ERR_CUDA;
+	}
+};
+
+#define SNB_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); } while (0)
+#define SNB_LAUNCHED(ctx) do { ++(ctx)->launches; cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, "kernel launch"); } while (0)

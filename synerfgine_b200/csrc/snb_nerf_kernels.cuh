@@ -1,0 +1,362 @@
+// synerfgine_b200 — NeRF layer kernels: ray generation + start jitter, the persistent fused
+// march -> encode -> MLP -> composite kernel, and the parity taps.
+//
+// Replaces (reference, src/testbed_nerf.cu): init_rays_with_payload_kernel_nerf :1855-1970, advance_pos_nerf_kernel
+// :334-384, compact_kernel_nerf :1830-1853, generate_next_nerf_network_inputs :790-837, composite_kernel_nerf
+// :577-788 / composite_kernel_nerf_alt :476-575, extract_from_payload :1578-1612, shade_kernel_nerf :1788-1828 and
+// the host loops NerfTracer::trace / trace_alt :2128-2401 (one D2H + stream sync per iteration there; none here).
+//
+// Design (DESIGN.md §"NeRF march"): rays are independent, so instead of a global wavefront with a compaction
+// kernel and a host round trip per iteration, a persistent grid of warps each owns 32 ray slots. A slot whose ray
+// finished is refilled from a global queue with one warp-aggregated atomicAdd (ballot + popc); every loop
+// iteration evaluates one sample per live slot: DDA skip -> hash-grid gather -> both MLPs on tensor cores ->
+// front-to-back composite in registers. Samples, features and network outputs never touch HBM; a finished ray
+// writes its pixel once. The per-ray batch counter (8 steps, MAX_STEPS_INBETWEEN_COMPACTION) is kept because
+// composite_kernel_nerf_alt rewinds payload.t at every batch boundary (src/testbed_nerf.cu:574).
+#pragma once
+#include "snb_camera.cuh"
+#include "snb_network.cuh"
+
+namespace snb {
+
+constexpr int kBatchSteps = 8;       // n_steps_between_compaction for <= 262144 alive rays (src/testbed_nerf.cu:2189-2190)
+constexpr int kFusedWarps = 4;
+constexpr int kFusedThreads = kFusedWarps * 32;
+
+struct NerfCounters { unsigned long long samples, rays, hits, batches; };
+
+struct NerfOut {                     // tile-sized output buffers
+	float4* fb;                      // rgba
+	float* depth;
+	float* positions;                // xyz per pixel (alt path) or nullptr
+};
+
+SNB_D float act_logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
+SNB_D float act_rgb(float v, int act) {
+	switch (act) {
+		case 0: return v;
+		case 1: return v > 0.0f ? v : 0.0f;
+		case 2: return act_logistic(v);
+		default: return expf(fminf(fmaxf(v, -10.0f), 10.0f));
+	}
+}
+SNB_D float act_density(float v, int act) {
+	switch (act) {
+		case 0: return v;
+		case 1: return v > 0.0f ? v : 0.0f;
+		case 2: return act_logistic(v);
+		default: return expf(v);
+	}
+}
+SNB_HD float dt_warp(float dt) { const float mx = kMinStep * (1 << 7); return (dt - kMinStep) / (mx - kMinStep); }
+SNB_HD float dt_unwarp(float dt) { const float mx = kMinStep * (1 << 7); return dt * (mx - kMinStep) + kMinStep; }
+
+SNB_D int tile_local_index(const DevView& v, uint32_t gidx) {
+	const int x = (int)(gidx % (uint32_t)v.width) - v.tx0, y = (int)(gidx / (uint32_t)v.width) - v.ty0;
+	return x + v.tw * y;
+}
+
+// ---- ray generation: one thread per tile pixel, 8x4 pixel patches per warp so queue neighbours are image neighbours ----
+__global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail) {
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int patches_x = (view.tw + 7) / 8;
+	const int patch = blockIdx.x * 4 + warp;
+	const int px = (patch % patches_x) * 8 + (lane & 7), py = (patch / patches_x) * 4 + (lane >> 3);
+	bool alive = false;
+	RayRec rec;
+	if (px < view.tw && py < view.th) {
+		const int x = view.tx0 + px, y = view.ty0 + py;
+		const int lidx = px + view.tw * py;
+		out.fb[lidx] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+		out.depth[lidx] = kMaxDepth;
+		if (out.positions) { out.positions[lidx * 3 + 0] = 0.0f; out.positions[lidx * 3 + 1] = 0.0f; out.positions[lidx * 3 + 2] = 0.0f; }
+		v3 o, d; float t;
+		alive = nerf_primary_ray(x, y, view, env, o, d, t);
+		const uint32_t idx = (uint32_t)x + (uint32_t)view.width * (uint32_t)y;
+		if (alive) {
+			// start jitter + skip to the first occupied cell (advance_pos_nerf)
+			const v3 idir = 1.0f / d;
+			t = advance_steps(t, env.st, ld_value(view.spp, idx * 786433u));
+			t = skip_to_occupied(t, o, d, idir, env);
+			alive = t < kMaxDepth;
+		}
+		rec.ox = o.x; rec.oy = o.y; rec.oz = o.z; rec.t = t; rec.dx = d.x; rec.dy = d.y; rec.dz = d.z; rec.idx = idx;
+	}
+	const unsigned int mask = __ballot_sync(0xFFFFFFFFu, alive);
+	if (mask == 0) return;
+	unsigned int base = 0;
+	if (lane == 0) base = atomicAdd(queue_tail, __popc(mask));
+	base = __shfl_sync(0xFFFFFFFFu, base, 0);
+	if (alive) {
+		float4* q = reinterpret_cast<float4*>(queue + base + __popc(mask & ((1u << lane) - 1u)));
+		q[0] = make_float4(rec.ox, rec.oy, rec.oz, rec.t);
+		q[1] = make_float4(rec.dx, rec.dy, rec.dz, __uint_as_float(rec.idx));
+	}
+}
+
+// Finished ray -> pixel (extract_from_payload for the sng path, shade_kernel_nerf for the stock path).
+SNB_D void write_pixel(const DevView& view, const NerfOut& out, bool alt, int render_mode, uint32_t idx, v3 dir, float t, float4 rgba, float depth) {
+	const int l = tile_local_index(view, idx);
+	float4 tmp = rgba;
+	if (alt) {
+		const v3 orig_pos = view.cam.c3 + dir * t;
+		if (render_mode == 4) { const float v = (float)fmax(0.0, 1.0 - (double)(depth / 3.0f)); tmp.x = tmp.y = tmp.z = v; }
+		else if (render_mode == 3) { tmp.x = srgb_to_linear(orig_pos.x * 0.5f + 0.5f); tmp.y = srgb_to_linear(orig_pos.y * 0.5f + 0.5f); tmp.z = srgb_to_linear(orig_pos.z * 0.5f + 0.5f); }
+		else { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+		if (out.positions) { out.positions[l * 3 + 0] = orig_pos.x; out.positions[l * 3 + 1] = orig_pos.y; out.positions[l * 3 + 2] = orig_pos.z; }
+	} else if (render_mode == 1) {
+		tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z);
+	}
+	out.fb[l] = tmp;   // frame buffer was cleared to 0 by ray generation: tmp + 0 * (1 - a)
+	if (tmp.w > 0.2f) out.depth[l] = depth;
+}
+
+// ---- the persistent fused kernel -----------------------------------------------------------------------------------
+// grid = SMs x resident CTAs, block = 4 warps; smem = fragment-ordered MLP weights (20 KB, shared by the CTA) +
+// per-warp staging tile (3.5 KB) + per-warp output tile (256 B).
+template <int F, bool ALT>
+__global__ void __launch_bounds__(kFusedThreads, 3)
+k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
+                   unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
+	__shared__ __align__(16) uint32_t s_w[kFragWords];
+	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
+	__shared__ GridDesc s_grid;   // level scales / resolutions / offsets staged once per CTA
+	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
+		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
+	for (int i = threadIdx.x; i < (int)(sizeof(GridDesc) / 4); i += kFusedThreads)
+		reinterpret_cast<uint32_t*>(&s_grid)[i] = reinterpret_cast<const uint32_t*>(&model.grid)[i];
+	__syncthreads();
+
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
+	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
+	const unsigned int n_rays = *queue_tail;
+	const MarchEnv& env = model.env;
+	const v3 cam_fwd = view.cam.c2;
+	const v3 aabb_diag = model.train_aabb.diag();
+
+	// per-slot ray state
+	v3 o = mk3(0, 0, 0), d = mk3(1, 0, 0), idir = mk3(1, 1, 1);
+	float t = 0.0f, depth = 0.0f, max_weight = 0.0f;
+	float4 rgba = make_float4(0, 0, 0, 0);
+	uint32_t idx = 0, step_i = 1;
+	int k = 0;
+	bool alive = false, drained = false;
+	uint32_t sh_frag[2][4];
+#pragma unroll
+	for (int m = 0; m < 2; ++m)
+#pragma unroll
+		for (int i = 0; i < 4; ++i) sh_frag[m][i] = 0u;
+	{ // zero the SH block once so never-filled rows hold finite values
+		const uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+		stage_sh_row(tile, lane, z);
+	}
+	unsigned long long n_samples = 0, n_hits = 0, n_launched = 0;
+
+	auto finish = [&]() {
+		alive = false;
+		if (step_i + kBatchSteps >= kMarchIter) return;   // died in the last possible iteration: never compacted into the hit list
+		if (ALT) t = depth / dot(cam_fwd, d);             // payload.t rewrite at the end of composite_kernel_nerf_alt
+		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth); ++n_hits; }
+	};
+
+	for (;;) {
+		// -- refill empty slots: one atomic per warp -----------------------------------------------------------------
+		const unsigned int need = __ballot_sync(0xFFFFFFFFu, !alive);
+		if (need && !drained) {
+			unsigned int base = 0;
+			if (lane == 0) base = atomicAdd(queue_head, __popc(need));
+			base = __shfl_sync(0xFFFFFFFFu, base, 0);
+			const unsigned int mine = base + __popc(need & ((1u << lane) - 1u));
+			if (!alive && mine < n_rays) {
+				const float4 q0 = __ldg(reinterpret_cast<const float4*>(queue + mine));
+				const float4 q1 = __ldg(reinterpret_cast<const float4*>(queue + mine) + 1);
+				o = mk3(q0.x, q0.y, q0.z); t = q0.w; d = mk3(q1.x, q1.y, q1.z); idx = __float_as_uint(q1.w);
+				idir = 1.0f / d;
+				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; alive = true;
+				++n_launched;
+				uint32_t sh[8];
+				encode_direction_sh4((d + 1.0f) * 0.5f, sh);   // warp_direction, nerf_device.cuh:290-292
+				stage_sh_row(tile, lane, sh);
+			}
+			if (base + __popc(need) >= n_rays) drained = true;
+			__syncwarp();
+			load_sh_frags(tile, lane, sh_frag);
+		}
+		if (__ballot_sync(0xFFFFFFFFu, alive) == 0) break;
+
+		// -- one march step per live slot ----------------------------------------------------------------------------
+		bool valid = false;
+		v3 wpos = mk3(0, 0, 0);
+		float wdt = 0.0f;
+		if (alive) {
+			t = skip_to_occupied(t, o, d, idir, env);
+			if (t >= kMaxDepth) {
+				finish();                                        // left the volume: batch ends short, ray is done
+			} else {
+				const float dt = step_size(t, env.st);
+				wpos = (o + d * t - model.train_aabb.lo) / aabb_diag;   // warp_position
+				wdt = dt_warp(dt);
+				t += dt;
+				valid = true;
+			}
+		}
+
+		// -- network: gather + both MLPs -------------------------------------------------------------------------------
+		uint32_t feat[16];
+#pragma unroll
+		for (int i = 0; i < 16; ++i) feat[i] = 0u;
+		if (valid) encode_position<F>(s_grid, model.grid_params, wpos, feat, nullptr);
+		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, feat, sh_frag);
+
+		// -- composite -------------------------------------------------------------------------------------------------
+		if (valid) {
+			++n_samples;
+			const __half2 rg = u2h2(net.x), bs = u2h2(net.y);
+			const v3 pos = model.train_aabb.lo + wpos * aabb_diag;   // unwarp_position
+			const float T = 1.f - rgba.w;
+			const float dt = dt_unwarp(wdt);
+			const float alpha = 1.f - expf(-act_density(__high2float(bs), model.density_act) * dt);
+			const float weight = alpha * T;
+			v3 rgb = mk3(act_rgb(__low2float(rg), model.rgb_act), act_rgb(__high2float(rg), model.rgb_act), act_rgb(__low2float(bs), model.rgb_act));
+			if (!ALT) {
+				if (render_mode == 3) rgb = (pos - 0.5f) / 2.0f + 0.5f;
+				else if (render_mode == 4) rgb = splat3(dot(cam_fwd, pos - o) * 1.0f);
+			}
+			rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
+			if (ALT) {
+				depth = dot(cam_fwd, pos - view.cam.c3);
+				if (weight > max_weight) max_weight = weight;
+			} else if (weight > max_weight) {
+				max_weight = weight;
+				depth = dot(cam_fwd, pos - view.cam.c3);
+			}
+			if (rgba.w > (1.0f - model.min_transmittance)) {
+				const float a = rgba.w;
+				rgba.x /= a; rgba.y /= a; rgba.z /= a; rgba.w /= a;
+				finish();
+			} else if (++k == kBatchSteps) {
+				// batch boundary: the sng compositor rewinds t to the last composited sample
+				if (ALT) t = depth / dot(cam_fwd, d);
+				k = 0;
+				step_i += kBatchSteps;
+				if (step_i >= kMarchIter) alive = false;         // iteration budget exhausted: ray is dropped, not written
+			}
+		}
+	}
+
+	// -- counters: one atomic per warp ----------------------------------------------------------------------------------
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		n_samples += __shfl_xor_sync(0xFFFFFFFFu, n_samples, s);
+		n_hits += __shfl_xor_sync(0xFFFFFFFFu, n_hits, s);
+		n_launched += __shfl_xor_sync(0xFFFFFFFFu, n_launched, s);
+	}
+	if (lane == 0 && counters) {
+		atomicAdd(&counters->samples, n_samples);
+		atomicAdd(&counters->hits, n_hits);
+		atomicAdd(&counters->rays, n_launched);
+	}
+}
+
+// ---- parity taps ---------------------------------------------------------------------------------------------------
+// Per-pixel march sample sequence with no early termination (what generate_next_nerf_network_inputs would emit).
+__global__ void __launch_bounds__(128) k_march_trace(DevView view, MarchEnv env, uint32_t max_samples, float* __restrict__ out_t, float* __restrict__ out_dt,
+                                                     uint32_t* __restrict__ out_cell, uint32_t* __restrict__ n_out, float* __restrict__ origin_dir) {
+	const uint32_t ray = blockIdx.x * blockDim.x + threadIdx.x;
+	if (ray >= (uint32_t)(view.width * view.height)) return;
+	const int x = (int)(ray % (uint32_t)view.width), y = (int)(ray / (uint32_t)view.width);
+	v3 o, d; float t;
+	bool alive = nerf_primary_ray(x, y, view, env, o, d, t);
+	if (alive) {
+		const v3 idir0 = 1.0f / d;
+		t = advance_steps(t, env.st, ld_value(view.spp, ray * 786433u));
+		t = skip_to_occupied(t, o, d, idir0, env);
+		alive = t < kMaxDepth;
+	}
+	if (origin_dir) { float* p = origin_dir + (size_t)ray * 6; p[0] = o.x; p[1] = o.y; p[2] = o.z; p[3] = d.x; p[4] = d.y; p[5] = d.z; }
+	uint32_t n = 0;
+	if (alive) {
+		const v3 idir = 1.0f / d;
+		for (; n < max_samples; ++n) {
+			t = skip_to_occupied(t, o, d, idir, env);
+			if (t >= kMaxDepth) break;
+			const float dt = step_size(t, env.st);
+			const v3 pos = o + d * t;
+			const uint32_t mip = clamp_mip(mip_of(pos), env);
+			const size_t at = (size_t)ray * max_samples + n;
+			out_t[at] = t; out_dt[at] = dt; out_cell[at] = (mip << 24) | (cascade_cell(pos, mip) & 0xFFFFFFu);
+			t += dt;
+		}
+	}
+	for (uint32_t j = n; j < max_samples; ++j) { const size_t at = (size_t)ray * max_samples + j; out_t[at] = 0.0f; out_dt[at] = 0.0f; out_cell[at] = 0xFFFFFFFFu; }
+	n_out[ray] = n;
+}
+
+// NerfNetwork inference on explicit NerfCoordinates (n x 7 floats) through the same warp evaluator as the fused kernel.
+template <int F>
+__global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel model, const float* __restrict__ coords, uint64_t n, uint16_t* __restrict__ out,
+                                                                     uint16_t* __restrict__ features, uint32_t* __restrict__ hash_idx) {
+	__shared__ __align__(16) uint32_t s_w[kFragWords];
+	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
+	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
+		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
+	__syncthreads();
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
+	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
+	const uint64_t n_tiles = (n + 31) / 32;
+	for (uint64_t tile_i = (uint64_t)blockIdx.x * kFusedWarps + warp; tile_i < n_tiles; tile_i += (uint64_t)gridDim.x * kFusedWarps) {
+		const uint64_t i = tile_i * 32 + lane;
+		const bool valid = i < n;
+		uint32_t feat[16], sh[8];
+#pragma unroll
+		for (int j = 0; j < 16; ++j) feat[j] = 0u;
+#pragma unroll
+		for (int j = 0; j < 8; ++j) sh[j] = 0u;
+		if (valid) {
+			const float* c = coords + i * 7;
+			const v3 p = mk3(c[0], c[1], c[2]), dir = mk3(c[4], c[5], c[6]);
+			if (hash_idx) encode_position<F>(model.grid, model.grid_params, p, feat, hash_idx + i * (uint64_t)(kFeat / F) * 8);
+			else encode_position<F>(model.grid, model.grid_params, p, feat, nullptr);
+			encode_direction_sh4(dir, sh);
+			if (features) {
+#pragma unroll
+				for (int j = 0; j < 16; ++j) reinterpret_cast<uint32_t*>(features)[i * 16 + j] = feat[j];
+			}
+		}
+		stage_sh_row(tile, lane, sh);
+		__syncwarp();
+		uint32_t sh_frag[2][4];
+		load_sh_frags(tile, lane, sh_frag);
+		const uint2 r = warp_network_eval(s_w, tile, out_tile, lane, feat, sh_frag);
+		if (valid) reinterpret_cast<uint2*>(out)[i] = r;
+	}
+}
+
+// ---- screen-space normals from the position buffer (write_normals_to_buffer, src/testbed_nerf.cu:1523-1576) -------------
+__global__ void __launch_bounds__(128) k_write_normals(int width, int height, const float* __restrict__ positions, float* __restrict__ normals) {
+	const int x = blockIdx.x * 16 + (threadIdx.x & 15), y = blockIdx.y * 8 + (threadIdx.x >> 4);
+	if (x >= width || y >= height) return;
+	const int offs[9][2] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}, {2, 0}, {0, 2}, {-2, 0}, {0, -2}, {1, 0}};
+	const int idx = x + width * y;
+	const v3 pos = mk3(positions[idx * 3], positions[idx * 3 + 1], positions[idx * 3 + 2]);
+	float factor = 0.0f;
+	v3 N = mk3(0, 0, 0);
+#pragma unroll
+	for (int k = 0; k < 8; ++k) {
+		const int tx = x + offs[k + 1][0], ty = y + offs[k + 1][1], bx = x + offs[k][0], by = y + offs[k][1];
+		if (tx >= width || tx < 0 || ty >= height || ty < 0 || bx >= width || bx < 0 || by >= height || by < 0) continue;
+		const float* tp = positions + (size_t)(ty * width + tx) * 3;
+		const float* bp = positions + (size_t)(by * width + bx) * 3;
+		const v3 T = mk3(tp[0], tp[1], tp[2]) - pos;
+		const v3 B = mk3(bp[0], bp[1], bp[2]) - pos;
+		N = N + normalize(cross(normalize(T), B));
+		factor += 1.0f;
+	}
+	N = factor == 0.0f ? N : N / factor;
+	N = normalize(N);
+	normals[idx * 3] = N.x; normals[idx * 3 + 1] = N.y; normals[idx * 3 + 2] = N.z;
+}
+
+} // namespace snb

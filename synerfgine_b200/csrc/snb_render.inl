@@ -1,0 +1,240 @@
+// synerfgine_b200 — render entry points (part of the snb_api.cu translation unit).
+
+static DevView make_view(const snb_view* v, const snb_tile* tile) {
+	DevView d;
+	d.cam.c0 = ld3(v->camera); d.cam.c1 = ld3(v->camera + 3); d.cam.c2 = ld3(v->camera + 6); d.cam.c3 = ld3(v->camera + 9);
+	d.focal.x = v->focal_length[0]; d.focal.y = v->focal_length[1];
+	d.center.x = v->screen_center[0]; d.center.y = v->screen_center[1];
+	d.width = v->width; d.height = v->height;
+	if (tile && tile->w > 0 && tile->h > 0) { d.tx0 = tile->x0; d.ty0 = tile->y0; d.tw = tile->w; d.th = tile->h; }
+	else { d.tx0 = 0; d.ty0 = 0; d.tw = v->width; d.th = v->height; }
+	d.spp = v->spp; d.snap = v->snap_to_pixel_centers;
+	d.pix_off = ld_pixel_offset(d.snap ? 0u : d.spp);
+	return d;
+}
+
+static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
+	if (!v || v->width <= 0 || v->height <= 0) return c->fail(SNB_ERR_ARG, "bad view");
+	if (t && t->w > 0 && t->h > 0 && (t->x0 < 0 || t->y0 < 0 || t->x0 + t->w > v->width || t->y0 + t->h > v->height)) return c->fail(SNB_ERR_ARG, "tile outside the view");
+	return SNB_OK;
+}
+
+template <int F, bool ALT>
+static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px) {
+	static int per_sm = 0;   // per template instance
+	if (per_sm == 0) {
+		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, 0));
+		per_sm = std::max(1, per_sm);
+	}
+	c->fused_blocks_per_sm = per_sm;
+	const int max_blocks = c->sm_count * per_sm;
+	const int want = (n_px + kFusedThreads - 1) / kFusedThreads;
+	const int blocks = std::max(1, std::min(max_blocks, want));
+	unsigned int* qctl = c->d_qctl.as<unsigned int>();
+	k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, dv, out, render_mode, c->d_queue.as<RayRec>(), qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+// NeRF layer into tile-sized buffers. alt = sng compositor (trace_alt) + positions.
+static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render_mode, float* fb, float* depth, float* positions) {
+	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
+	const int n_px = dv.tw * dv.th;
+	SNB_CUDA(c, c->d_queue.reserve((size_t)n_px * sizeof(RayRec)));
+	SNB_CUDA(c, cudaMemsetAsync(c->d_qctl.p, 0, 8, c->stream));
+	SNB_CUDA(c, cudaMemsetAsync(c->d_counters.p, 0, sizeof(NerfCounters), c->stream));
+	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
+	unsigned int* qctl = c->d_qctl.as<unsigned int>();
+	const int patches = ((dv.tw + 7) / 8) * ((dv.th + 3) / 4);
+	k_nerf_raygen<<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, c->d_queue.as<RayRec>(), qctl);
+	SNB_LAUNCHED(c);
+	int rc;
+	switch (c->feat_per_level) {
+		case 1: rc = alt ? launch_fused<1, true>(c, dv, out, render_mode, n_px) : launch_fused<1, false>(c, dv, out, render_mode, n_px); break;
+		case 2: rc = alt ? launch_fused<2, true>(c, dv, out, render_mode, n_px) : launch_fused<2, false>(c, dv, out, render_mode, n_px); break;
+		case 4: rc = alt ? launch_fused<4, true>(c, dv, out, render_mode, n_px) : launch_fused<4, false>(c, dv, out, render_mode, n_px); break;
+		default: rc = alt ? launch_fused<8, true>(c, dv, out, render_mode, n_px) : launch_fused<8, false>(c, dv, out, render_mode, n_px); break;
+	}
+	return rc;
+}
+
+static int ensure_rng(snb_ctx* c, const DevView& syn, const DevView& nerf) {
+	const bool same = !c->rng_dirty && c->rng_w == syn.width && c->rng_h == syn.height && c->rng_tx0 == syn.tx0 && c->rng_ty0 == syn.ty0 &&
+	                  c->rng_tw == syn.tw && c->rng_th == syn.th && c->rng_scale == syn.width / nerf.width;
+	if (same) return SNB_OK;
+	const uint32_t n_syn = (uint32_t)(syn.tw * syn.th), n_nerf = (uint32_t)(nerf.tw * nerf.th);
+	SNB_CUDA(c, c->d_rng_syn.reserve((size_t)n_syn * sizeof(Rng)));
+	SNB_CUDA(c, c->d_rng_nerf.reserve((size_t)n_nerf * sizeof(Rng)));
+	k_init_rng<<<(n_syn + 127) / 128, 128, 0, c->stream>>>(n_syn, (unsigned long long)c->rng_seed, syn.width, syn.tx0, syn.ty0, syn.tw, c->d_rng_syn.as<Rng>());
+	SNB_LAUNCHED(c);
+	k_init_rng<<<(n_nerf + 127) / 128, 128, 0, c->stream>>>(n_nerf, (unsigned long long)c->rng_seed, nerf.width, nerf.tx0, nerf.ty0, nerf.tw, c->d_rng_nerf.as<Rng>());
+	SNB_LAUNCHED(c);
+	c->rng_dirty = false; c->rng_w = syn.width; c->rng_h = syn.height; c->rng_tx0 = syn.tx0; c->rng_ty0 = syn.ty0; c->rng_tw = syn.tw; c->rng_th = syn.th;
+	c->rng_scale = syn.width / nerf.width;
+	c->syn_reset = true;
+	return SNB_OK;
+}
+
+static RtParams make_rt(const snb_rt_params* rt) {
+	RtParams r;
+	r.n_steps = rt->n_steps; r.samples = rt->samples; r.bounces = rt->bounces; r.shadow_iters = rt->shadow_iters;
+	r.lens = rt->lens_angle_constant; r.depth_offset = rt->depth_offset; r.syn_shadow_factor = rt->syn_shadow_factor;
+	r.view_nerf_shadow = rt->view_nerf_shadow; r.buffer_type = rt->buffer_type;
+	return r;
+}
+
+// Mesh layer into the context's syn buffers (tile-sized).
+static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt) {
+	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
+	if (rt->samples == 0 || rt->bounces == 0 || rt->shadow_iters == 0) return c->fail(SNB_ERR_ARG, "samples, bounces and shadow_iters must be >= 1");
+	const uint32_t n = (uint32_t)(dv.tw * dv.th);
+	if (c->syn_w != dv.tw || c->syn_h != dv.th) { c->syn_reset = true; c->syn_w = dv.tw; c->syn_h = dv.th; }
+	SNB_CUDA(c, c->d_syn_origins.reserve((size_t)n * 12));
+	SNB_CUDA(c, c->d_syn_dirs.reserve((size_t)n * 12));
+	SNB_CUDA(c, c->d_syn_rgba.reserve((size_t)n * 16));
+	SNB_CUDA(c, c->d_syn_depth.reserve((size_t)n * 4));
+	const dim3 grid2((dv.tw + 15) / 16, (dv.th + 7) / 8);
+	if (c->syn_reset) {
+		k_syn_raygen<<<grid2, 128, 0, c->stream>>>(dv, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), nullptr, nullptr, c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
+		SNB_LAUNCHED(c);
+		c->syn_reset = false;
+	}
+	k_raytrace<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
+	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+// Normals + mesh shadows on the NeRF layer (tile-sized buffers; window reads stop at the tile edge like at the image edge).
+static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int render_mode, float* fb, float* positions, float* normals) {
+	const dim3 grid2((dv.tw + 15) / 16, (dv.th + 7) / 8);
+	k_write_normals<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, positions, normals);
+	SNB_LAUNCHED(c);
+	if (rt->show_shadow_on_nerf) {
+		const uint32_t n = (uint32_t)(dv.tw * dv.th);
+		SNB_CUDA(c, c->d_terms.reserve((size_t)n * 4));
+		MarchEnv env = c->model.env; env.min_mip = 0;
+		k_nerf_shadow_terms<<<(n + 127) / 128, 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
+		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>());
+		SNB_LAUNCHED(c);
+		k_nerf_shadow_apply<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, rt->nerf_shadow_kernel / 2, rt->nerf_shadow_intensity, render_mode, c->d_terms.as<float>(),
+		                                                  reinterpret_cast<float4*>(fb), nullptr);
+		SNB_LAUNCHED(c);
+	}
+	return SNB_OK;
+}
+
+static DevView nerf_view_of(const DevView& syn, int scale) {
+	DevView n = syn;
+	if (scale > 1) {
+		n.width = syn.width / scale; n.height = syn.height / scale;
+		n.tx0 = syn.tx0 / scale; n.ty0 = syn.ty0 / scale; n.tw = syn.tw / scale; n.th = syn.th / scale;
+		n.focal.x = syn.focal.x / (float)scale; n.focal.y = syn.focal.y / (float)scale;
+	}
+	return n;
+}
+
+extern "C" {
+
+int snb_render_nerf(snb_ctx* c, const snb_view* view, const snb_tile* tile, int render_mode, float* fb, float* depth) {
+	if (!c || !fb || !depth) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	return render_nerf_layer(c, make_view(view, tile), false, render_mode, fb, depth, nullptr);
+}
+
+int snb_render_syn(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* syn_rgba, float* syn_depth) {
+	if (!c || !rt) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const DevView dv = make_view(view, tile);
+	const int scale = std::max(1, rt->syn_px_scale);
+	rc = ensure_rng(c, dv, nerf_view_of(dv, scale)); if (rc) return rc;
+	rc = render_syn_layer(c, dv, rt); if (rc) return rc;
+	const size_t n = (size_t)dv.tw * dv.th;
+	if (syn_rgba) SNB_CUDA(c, cudaMemcpyAsync(syn_rgba, c->d_syn_rgba.p, n * 16, cudaMemcpyDeviceToDevice, c->stream));
+	if (syn_depth) SNB_CUDA(c, cudaMemcpyAsync(syn_depth, c->d_syn_depth.p, n * 4, cudaMemcpyDeviceToDevice, c->stream));
+	return SNB_OK;
+}
+
+int snb_render_nerf_with_buffers(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, int render_mode,
+                                 float* fb, float* depth, float* positions, float* normals) {
+	if (!c || !rt || !fb || !depth) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const DevView dv = make_view(view, tile);
+	const size_t n = (size_t)dv.tw * dv.th;
+	if (!positions) { SNB_CUDA(c, c->d_positions.reserve(n * 12)); positions = c->d_positions.as<float>(); }
+	if (!normals) { SNB_CUDA(c, c->d_normals.reserve(n * 12)); normals = c->d_normals.as<float>(); }
+	// RNG states of the NeRF layer are per NeRF pixel; (re)seeded on resize like Engine::resize (engine.cu:236-255).
+	DevView syn = dv; const int scale = std::max(1, rt->syn_px_scale);
+	if (scale > 1) { syn.width *= scale; syn.height *= scale; syn.tx0 *= scale; syn.ty0 *= scale; syn.tw *= scale; syn.th *= scale; }
+	rc = ensure_rng(c, syn, dv); if (rc) return rc;
+	rc = render_nerf_layer(c, dv, true, render_mode, fb, depth, positions); if (rc) return rc;
+	return nerf_post(c, dv, rt, render_mode, fb, positions, normals);
+}
+
+int snb_overlay(snb_ctx* c, int syn_w, int syn_h, const snb_rt_params* rt, const float* syn_rgba, const float* syn_depth, const float* nerf_rgba,
+                const float* nerf_depth, float* out_rgba, float* out_depth) {
+	if (!c || !rt || !syn_rgba || !syn_depth || !nerf_rgba || !nerf_depth || !out_rgba || syn_w <= 0 || syn_h <= 0) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const dim3 grid2((syn_w + 15) / 16, (syn_h + 7) / 8);
+	k_overlay<<<grid2, 128, 0, c->stream>>>(syn_w, syn_h, std::max(1, rt->syn_px_scale), reinterpret_cast<const float4*>(syn_rgba), syn_depth,
+	                                        reinterpret_cast<const float4*>(nerf_rgba), nerf_depth, rt->show_nerf, 1, rt->tonemap_curve, rt->exposure, rt->depth_offset,
+	                                        reinterpret_cast<float4*>(out_rgba), out_depth);
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+int snb_accumulate_tonemap(snb_ctx* c, int n_pixels, const float* frame, float* accum, uint32_t spp, int cs_srgb, int out_srgb, float exposure,
+                           const float* bg, int curve, float* out) {
+	if (!c || !frame || !accum || !bg || !out || n_pixels <= 0) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	k_accumulate_tonemap<<<(n_pixels + 127) / 128, 128, 0, c->stream>>>(n_pixels, reinterpret_cast<const float4*>(frame), reinterpret_cast<float4*>(accum), spp, cs_srgb, out_srgb,
+	                                                                   exposure, make_float4(bg[0], bg[1], bg[2], bg[3]), curve, reinterpret_cast<float4*>(out));
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba, float* out_depth) {
+	if (!c || !rt || !out_rgba) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const int scale = std::max(1, rt->syn_px_scale);
+	const DevView syn = make_view(view, tile);
+	if (scale > 1 && (syn.width % scale || syn.height % scale || syn.tx0 % scale || syn.ty0 % scale || syn.tw % scale || syn.th % scale))
+		return c->fail(SNB_ERR_ARG, "view and tile must be multiples of syn_px_scale");
+	const DevView nerf = nerf_view_of(syn, scale);
+	const size_t n_nerf = (size_t)nerf.tw * nerf.th;
+	rc = ensure_rng(c, syn, nerf); if (rc) return rc;
+	// 1. mesh layer (RayTracer::render)
+	rc = render_syn_layer(c, syn, rt); if (rc) return rc;
+	// 2. NeRF layer with mesh shadows (Testbed::render sng overload)
+	SNB_CUDA(c, c->d_nerf_fb.reserve(n_nerf * 16));
+	SNB_CUDA(c, c->d_nerf_depth.reserve(n_nerf * 4));
+	if (rt->show_nerf) {
+		SNB_CUDA(c, c->d_positions.reserve(n_nerf * 12));
+		SNB_CUDA(c, c->d_normals.reserve(n_nerf * 12));
+		rc = render_nerf_layer(c, nerf, true, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), c->d_positions.as<float>()); if (rc) return rc;
+		rc = nerf_post(c, nerf, rt, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_positions.as<float>(), c->d_normals.as<float>()); if (rc) return rc;
+	}
+	// 3. overlay (RayTracer::overlay), output colour space sRGB (engine.cu:406)
+	return snb_overlay(c, syn.tw, syn.th, rt, c->d_syn_rgba.as<float>(), c->d_syn_depth.as<float>(), c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), out_rgba, out_depth);
+}
+
+int snb_frame_host(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_host, float* out_depth_host) {
+	if (!c || !out_rgba_host) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	const DevView dv = make_view(view, tile);
+	const size_t n = (size_t)dv.tw * dv.th;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, c->d_out_rgba.reserve(n * 16));
+	SNB_CUDA(c, c->d_out_depth.reserve(n * 4));
+	rc = snb_frame(c, view, tile, rt, c->d_out_rgba.as<float>(), c->d_out_depth.as<float>()); if (rc) return rc;
+	SNB_CUDA(c, cudaMemcpyAsync(out_rgba_host, c->d_out_rgba.p, n * 16, cudaMemcpyDeviceToHost, c->stream));
+	if (out_depth_host) SNB_CUDA(c, cudaMemcpyAsync(out_depth_host, c->d_out_depth.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	return SNB_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,118 @@
+// synerfgine_b200 — parity taps, counters and the occupancy bitfield builder (part of the snb_api.cu translation unit).
+
+namespace snb {
+
+SNB_HD uint32_t compact3(uint32_t x) { // inverse of spread3 (tcnn morton3D_invert)
+	x &= 0x49249249u;
+	x = (x | (x >> 2)) & 0xc30c30c3u;
+	x = (x | (x >> 4)) & 0x0f00f00fu;
+	x = (x | (x >> 8)) & 0xff0000ffu;
+	x = (x | (x >> 16)) & 0x0000ffffu;
+	return x;
+}
+
+// density > min(0.01, mean) -> one bit per cell, 8 cells per byte; cascades above max_cascade are zeroed.
+__global__ void __launch_bounds__(128) k_density_to_bits(uint32_t n_bytes, uint32_t n_nonzero_bytes, const float* __restrict__ density, float thresh, uint8_t* __restrict__ bits_out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_bytes) return;
+	if (i >= n_nonzero_bytes) { bits_out[i] = 0; return; }
+	uint8_t bits = 0;
+#pragma unroll
+	for (int j = 0; j < 8; ++j) bits |= density[(size_t)i * 8 + j] > thresh ? (uint8_t)(1u << j) : (uint8_t)0;
+	bits_out[i] = bits;
+}
+
+// 2x2x2 OR-pool of one cascade into the centre octant of the next (Morton order on both sides).
+__global__ void __launch_bounds__(128) k_bits_max_pool(uint32_t n_bytes_next_octant, const uint8_t* __restrict__ prev, uint8_t* __restrict__ next) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_bytes_next_octant) return;
+	uint8_t bits = 0;
+#pragma unroll
+	for (int j = 0; j < 8; ++j) bits |= prev[(size_t)i * 8 + j] > 0 ? (uint8_t)(1u << j) : (uint8_t)0;
+	const uint32_t x = compact3(i >> 0) + kGridSize / 8, y = compact3(i >> 1) + kGridSize / 8, z = compact3(i >> 2) + kGridSize / 8;
+	next[morton3(x, y, z)] |= bits;
+}
+
+} // namespace snb
+
+extern "C" {
+
+int snb_march_trace(snb_ctx* c, const snb_view* view, uint32_t max_samples, float* t_dev, float* dt_dev, uint32_t* cell_dev, uint32_t* n_dev, float* origin_dir_dev) {
+	if (!c || !t_dev || !dt_dev || !cell_dev || !n_dev || max_samples == 0) return SNB_ERR_ARG;
+	int rc = check_view(c, view, nullptr); if (rc) return rc;
+	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const DevView dv = make_view(view, nullptr);
+	const uint32_t n = (uint32_t)(dv.width * dv.height);
+	k_march_trace<<<(n + 127) / 128, 128, 0, c->stream>>>(dv, c->model.env, max_samples, t_dev, dt_dev, cell_dev, n_dev, origin_dir_dev);
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+int snb_network_inference(snb_ctx* c, const float* coords_dev, uint64_t n, uint16_t* out_dev, uint16_t* features_dev, uint32_t* hash_idx_dev) {
+	if (!c || !coords_dev || !out_dev) return SNB_ERR_ARG;
+	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model");
+	if (n == 0) return SNB_OK;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const uint64_t tiles = (n + 31) / 32;
+	const int blocks = (int)std::min<uint64_t>((tiles + kFusedWarps - 1) / kFusedWarps, (uint64_t)c->sm_count * 8);
+	switch (c->feat_per_level) {
+		case 1: k_network_inference<1><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		case 2: k_network_inference<2><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		case 4: k_network_inference<4><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		default: k_network_inference<8><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+	}
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+int snb_trace_rays(snb_ctx* c, const float* rays_dev, uint32_t n, int32_t* obj_id_dev, int32_t* tri_id_dev, float* t_dev) {
+	if (!c || !rays_dev || !obj_id_dev || !tri_id_dev || !t_dev) return SNB_ERR_ARG;
+	if (n == 0) return SNB_OK;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	k_trace_rays<<<(n + 127) / 128, 128, 0, c->stream>>>(n, rays_dev, c->scene, obj_id_dev, tri_id_dev, t_dev);
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+int snb_get_counters(snb_ctx* c, uint64_t* out4) {
+	if (!c || !out4) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	NerfCounters h;
+	SNB_CUDA(c, cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	out4[0] = h.samples; out4[1] = h.rays; out4[2] = h.hits; out4[3] = h.batches;
+	return SNB_OK;
+}
+
+int snb_density_to_bitfield(snb_ctx* c, const float* density_host, uint32_t max_cascade, uint8_t* bitfield_out_host) {
+	if (!c || !density_host || !bitfield_out_host || max_cascade >= kCascades) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	const size_t n_cells = (size_t)kGridCells * (max_cascade + 1);
+	// mean of max(d, 0) over cascade 0 (update_density_grid_mean_and_bitfield reduces NERF_GRID_N_CELLS elements)
+	double acc = 0.0;
+	for (uint32_t i = 0; i < kGridCells; ++i) acc += (double)std::max(density_host[i], 0.0f);
+	const float mean = (float)(acc / (double)kGridCells);
+	const float thresh = std::min(0.01f, mean);   // NERF_MIN_OPTICAL_THICKNESS
+	DevBuf d_density, d_bits;
+	const uint32_t n_bytes = kGridCells / 8 * kCascades;
+	cudaError_t e = d_density.reserve(n_cells * 4);
+	if (e == cudaSuccess) e = d_bits.reserve(n_bytes);
+	if (e != cudaSuccess) { d_density.release(); d_bits.release(); return c->cuda_fail(e, "bitfield scratch"); }
+	cudaMemcpyAsync(d_density.p, density_host, n_cells * 4, cudaMemcpyHostToDevice, c->stream);
+	k_density_to_bits<<<(n_bytes + 127) / 128, 128, 0, c->stream>>>(n_bytes, kGridCells / 8 * (max_cascade + 1), d_density.as<float>(), thresh, d_bits.as<uint8_t>());
+	++c->launches;
+	for (uint32_t level = 1; level < kCascades; ++level) {
+		const uint32_t n = kGridCells / 64;
+		k_bits_max_pool<<<(n + 127) / 128, 128, 0, c->stream>>>(n, d_bits.as<uint8_t>() + (size_t)(level - 1) * kGridCells / 8, d_bits.as<uint8_t>() + (size_t)level * kGridCells / 8);
+		++c->launches;
+	}
+	cudaMemcpyAsync(bitfield_out_host, d_bits.p, n_bytes, cudaMemcpyDeviceToHost, c->stream);
+	e = cudaStreamSynchronize(c->stream);
+	if (e == cudaSuccess) e = cudaGetLastError();
+	d_density.release(); d_bits.release();
+	if (e != cudaSuccess) return c->cuda_fail(e, "snb_density_to_bitfield");
+	return SNB_OK;
+}
+
+} // extern "C"
