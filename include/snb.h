@@ -177,6 +177,9 @@ int snb_scene_get(const snb_scene* s, snb_object* objects, snb_material* materia
 /* camera block: view dir, look-at, zoom, vo_scale + keyframe path; frame index advances CamPath (cam_path.cuh:116-142). */
 int snb_scene_camera(const snb_scene* s, float* view3, float* at3, float* zoom, float* vo_scale, uint32_t* n_keyframes);
 int snb_scene_camera_at(const snb_scene* s, uint32_t frame, uint32_t total_frames, float* view3, float* at3, float* zoom);
+/* ≙ Testbed::reset_camera + set_view_dir + set_look_at + set_scale (src/testbed.cu:405-425,470-492) as Engine::init
+ * applies the JSON camera block (engine.cu:148-151): camera matrix (mat4x3, column-major) out. */
+int snb_camera_from_view(const float* view3, const float* at3, float zoom, float* out12);
 /* ≙ VirtualObject::next_frame / Light::next_frame (virtual_object.cuh:53-64; light.cuh:40-49). */
 int snb_scene_advance(snb_scene* s);
 /* ≙ TriangleBvhWithBranchingFactor<2>::build (src/triangle_bvh.cu:615-718); reorders tris in place. */
