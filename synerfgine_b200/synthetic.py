@@ -102,7 +102,7 @@ def density_to_bitfield(density, max_cascade):
 class SyntheticModel:
     """Arrays + metadata of one model; ``desc()`` fills the ctypes struct shared by libsnb.so and the oracle."""
 
-    def __init__(self, n_levels=16, n_feat=2, log2_T=19, base_res=16, aabb_scale=4, seed=1337, density_gain=6.0, feature_amp=0.5,
+    def __init__(self, n_levels=16, n_feat=2, log2_T=19, base_res=16, aabb_scale=4, seed=1337, density_gain=8.0, rgb_gain=8.0, feature_amp=0.5, feature_mean=0.0,
                  occupancy=True, rgb_activation=2, density_activation=3, min_transmittance=0.01):
         assert n_levels * n_feat == 32
         self.n_levels, self.n_feat, self.log2_T, self.base_res, self.aabb_scale = n_levels, n_feat, log2_T, base_res, aabb_scale
@@ -114,9 +114,10 @@ class SyntheticModel:
             s = math.sqrt(6.0 / (n_in + n_out))
             return rng.uniform(-s, s, size=(n_out, n_in)).astype(np.float32)
         dw1, dw2, rw1, rw2, rw3 = xavier(64, 32), xavier(16, 64), xavier(64, 32), xavier(64, 64), xavier(16, 64)
-        dw2[0] *= density_gain          # widen the log-density so rays saturate inside occupied cells
+        dw2[0] = np.abs(dw2[0]) * density_gain   # positive, amplified log-density head so rays saturate inside occupied cells
+        rw3[:3] *= rgb_gain              # spread the colours away from logistic(0)
         rw3[3:] = 0.0                    # padded outputs of the rgb head (3 live rows)
-        grid = rng.uniform(-feature_amp, feature_amp, size=self.offsets[-1] * n_feat).astype(np.float32)
+        grid = (rng.uniform(-feature_amp, feature_amp, size=self.offsets[-1] * n_feat) + feature_mean).astype(np.float32)
         self.params = np.concatenate([w.reshape(-1) for w in (dw1, dw2, rw1, rw2, rw3)] + [grid]).astype(np.float16)
         assert self.params.size == MLP_HALVES + self.offsets[-1] * n_feat
         self.max_cascade = int(round(math.log2(aabb_scale))) if aabb_scale > 1 else 0

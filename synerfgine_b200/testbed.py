@@ -1,0 +1,243 @@
+"""Python surface mirroring the reference's ``pyngp.Testbed`` render entry (src/python_api.cu:125-205,415-560) and the
+``sng::Engine`` object (include/synerfgine/engine.cuh:22-33), on top of the C ABI in include/snb.h.
+
+torch is used only to own device memory and streams; all rendering happens in libsnb.so.
+"""
+import ctypes as C
+import math
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Light, Material, Object, RtParams, Tile, View
+
+
+def _fp(a):
+    return a.ctypes.data_as(_lib.pf32)
+
+
+class Testbed:
+    """NeRF-only render entry: ``render(width, height, spp, linear)`` -> float32 [H, W, 4] like pyngp.Testbed.render."""
+
+    def __init__(self, device=0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("synerfgine_b200 needs a CUDA device (no CPU fallback)")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self.ctx = C.c_void_p()
+        rc = self.lib.snb_create(device, None, C.byref(self.ctx))
+        if rc != 0:
+            raise _lib.SnbError(f"snb_create failed ({rc})")
+        # Testbed::reset_camera defaults (src/testbed.cu:470-492)
+        self.fov_axis = 1
+        self.zoom = 1.0
+        self.screen_center = (0.5, 0.5)
+        self.relative_focal_length = 0.5 / math.tan(0.5 * 50.625 * math.pi / 180.0)
+        self.scale = 1.5
+        self.camera_matrix = np.array([[1, 0, 0], [0, -1, 0], [0, 0, -1], [0.5, 0.5, 0.5 + 1.5]], dtype=np.float32)  # columns
+        self.exposure = 0.0
+        self.background_color = (0.0, 0.0, 0.0, 0.0)
+        self.render_mode = 1        # ERenderMode::Shade
+        self.tonemap_curve = 0
+        self.snap_to_pixel_centers = True
+        self.model = None
+        self._accum = None
+        self._spp = 0
+
+    def close(self):
+        if self.ctx:
+            self.lib.snb_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        _lib.check(self.lib, self.ctx, rc, what)
+
+    # ---- inputs --------------------------------------------------------------------------------------------------
+    def set_model(self, model):
+        """model: synthetic.SyntheticModel (or anything with .desc()); ≙ the state load_snapshot leaves in Testbed."""
+        self.model = model
+        d = model.desc()
+        self._check(self.lib.snb_set_model(self.ctx, C.byref(d)), "snb_set_model")
+
+    def load_snapshot(self, path):
+        raise NotImplementedError(".ingp/.msgpack snapshot container is SURVEY §8(f) rank 2 (next rows); use set_model()")
+
+    def set_camera_from_view(self, view, at, zoom):
+        """≙ Engine::init applying the JSON camera block: set_view_dir, set_look_at, set_scale."""
+        out = np.zeros(12, dtype=np.float32)
+        v = np.asarray(view, dtype=np.float32); a = np.asarray(at, dtype=np.float32)
+        rc = self.lib.snb_camera_from_view(_fp(v), _fp(a), float(zoom), _fp(out))
+        if rc != 0:
+            raise _lib.SnbError("snb_camera_from_view failed")
+        self.camera_matrix = out.reshape(4, 3).copy()
+        self.scale = float(zoom)
+
+    def calc_focal_length(self, width, height):
+        res = (width, height)[self.fov_axis]
+        f = np.float32(self.relative_focal_length) * np.float32(res) * np.float32(self.zoom)
+        return (float(f), float(f))
+
+    def make_view(self, width, height, spp=0):
+        v = View()
+        v.camera[:] = [float(x) for x in np.asarray(self.camera_matrix, dtype=np.float32).reshape(-1)]
+        v.focal_length[:] = self.calc_focal_length(width, height)
+        sc = [(0.5 - c) * self.zoom + 0.5 for c in self.screen_center]   # render_screen_center, src/testbed.cu:4137-4140
+        v.screen_center[:] = sc
+        v.width, v.height, v.spp = width, height, spp
+        v.snap_to_pixel_centers = 1 if self.snap_to_pixel_centers else 0
+        return v
+
+    # ---- render ---------------------------------------------------------------------------------------------------
+    def render_nerf_raw(self, width, height, spp_index=0, render_mode=None, tile=None):
+        """One NeRF sample frame (render_nerf): returns (rgba [h,w,4], depth [h,w]) device tensors, linear colours."""
+        v = self.make_view(width, height, spp_index)
+        w, h = (tile.w, tile.h) if tile is not None else (width, height)
+        fb = torch.empty((h, w, 4), dtype=torch.float32, device=self.device)
+        depth = torch.empty((h, w), dtype=torch.float32, device=self.device)
+        mode = self.render_mode if render_mode is None else render_mode
+        self._check(self.lib.snb_render_nerf(self.ctx, C.byref(v), C.byref(tile) if tile is not None else None, mode, fb.data_ptr(), depth.data_ptr()),
+                    "snb_render_nerf")
+        self._check(self.lib.snb_sync(self.ctx), "snb_sync")
+        return fb, depth
+
+    def render(self, width=1920, height=1080, spp=1, linear=True, start_t=-1.0, end_t=-1.0, fps=30.0, shutter_fraction=1.0):
+        """≙ pyngp.Testbed.render: accumulate ``spp`` samples, tonemap, return float32 ndarray [H, W, 4]."""
+        if start_t >= 0 or end_t >= 0:
+            raise NotImplementedError("camera-path motion blur (start_t/end_t) is SURVEY §8(f) rank 4")
+        n = width * height
+        accum = torch.zeros((n, 4), dtype=torch.float32, device=self.device)
+        out = torch.empty((n, 4), dtype=torch.float32, device=self.device)
+        bg = np.asarray(self.background_color, dtype=np.float32)
+        for i in range(spp):
+            fb, _ = self.render_nerf_raw(width, height, spp_index=i)
+            self._check(self.lib.snb_accumulate_tonemap(self.ctx, n, fb.data_ptr(), accum.data_ptr(), i, 0, 0 if linear else 1, float(self.exposure),
+                                                        _fp(bg), self.tonemap_curve, out.data_ptr()), "snb_accumulate_tonemap")
+        self._check(self.lib.snb_sync(self.ctx), "snb_sync")
+        return out.reshape(height, width, 4).cpu().numpy()
+
+    def counters(self):
+        out = (C.c_uint64 * 4)()
+        self._check(self.lib.snb_get_counters(self.ctx, out), "snb_get_counters")
+        return {"samples": out[0], "rays": out[1], "hits": out[2]}
+
+    def launch_count(self):
+        return int(self.lib.snb_launch_count(self.ctx))
+
+
+class Scene:
+    """Parsed virtual-scene JSON (host side): objects with BVHs, materials, lights, rendering settings, camera path."""
+
+    def __init__(self, json_text, base_dir=None):
+        self.lib = _lib.load()
+        self.handle = C.c_void_p()
+        err = C.create_string_buffer(512)
+        rc = self.lib.snb_scene_load_json(json_text.encode(), base_dir.encode() if base_dir else None, C.byref(self.handle), err, 512)
+        if rc != 0:
+            raise _lib.SnbError(f"scene JSON: {err.value.decode()}")
+        self.refresh()
+        view = (C.c_float * 3)(); at = (C.c_float * 3)(); zoom = C.c_float(); vo = C.c_float(); nk = C.c_uint32()
+        self.lib.snb_scene_camera(self.handle, view, at, C.byref(zoom), C.byref(vo), C.byref(nk))
+        self.view_dir, self.at_pos, self.zoom, self.vo_scale, self.n_keyframes = list(view), list(at), zoom.value, vo.value, nk.value
+
+    @classmethod
+    def from_file(cls, path, base_dir=None):
+        with open(path) as f:
+            return cls(f.read(), base_dir if base_dir is not None else os.path.dirname(os.path.abspath(path)))
+
+    def refresh(self):
+        no, nm, nl = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self.lib.snb_scene_counts(self.handle, C.byref(no), C.byref(nm), C.byref(nl))
+        self.objects = (Object * max(1, no.value))(); self.materials = (Material * max(1, nm.value))(); self.lights = (Light * max(1, nl.value))()
+        self.n_objects, self.n_materials, self.n_lights = no.value, nm.value, nl.value
+        self.rt = RtParams()
+        self.lib.snb_scene_get(self.handle, self.objects, self.materials, self.lights, C.byref(self.rt))
+
+    def camera_at(self, frame, total_frames=0):
+        view = (C.c_float * 3)(); at = (C.c_float * 3)(); zoom = C.c_float()
+        rc = self.lib.snb_scene_camera_at(self.handle, frame, total_frames, view, at, C.byref(zoom))
+        if rc != 0:
+            raise _lib.SnbError("scene has no camera path")
+        return list(view), list(at), zoom.value
+
+    def advance(self):
+        self.lib.snb_scene_advance(self.handle)
+        self.refresh()
+
+    def __del__(self):
+        try:
+            if self.handle:
+                self.lib.snb_scene_free(self.handle)
+                self.handle = C.c_void_p()
+        except Exception:
+            pass
+
+
+class Engine:
+    """≙ sng::Engine minus GLFW/ImGui/GL: init(w, h, testbed), set_virtual_world(path), frame() -> final RGBA + depth."""
+
+    def __init__(self):
+        self.testbed = None
+        self.scene = None
+        self.rt = None
+        self.width = self.height = 0
+        self.frame_index = 0
+        self.tile = None
+
+    def set_virtual_world(self, config_fp, base_dir=None):
+        self.scene = Scene.from_file(config_fp, base_dir)
+        self.rt = self.scene.rt.copy()
+
+    def set_virtual_world_json(self, json_text, base_dir=None):
+        self.scene = Scene(json_text, base_dir)
+        self.rt = self.scene.rt.copy()
+
+    def init(self, res_width, res_height, testbed, tile=None):
+        self.testbed, self.width, self.height, self.tile = testbed, res_width, res_height, tile
+        tb, sc = testbed, self.scene
+        if sc is None:
+            raise RuntimeError("set_virtual_world first")
+        if any(x != 0.0 for x in sc.view_dir):
+            tb.set_camera_from_view(sc.view_dir, sc.at_pos, sc.zoom)
+        tb.exposure = self.rt.exposure
+        self.rt.tonemap_curve = tb.tonemap_curve
+        tb._check(tb.lib.snb_set_scene(tb.ctx, sc.objects, sc.n_objects, sc.materials, sc.n_materials, sc.lights, sc.n_lights), "snb_set_scene")
+        tb._check(tb.lib.snb_seed_rng(tb.ctx, 1999), "snb_seed_rng")
+        w, h = (tile.w, tile.h) if tile is not None else (res_width, res_height)
+        self.out_rgba = torch.empty((h, w, 4), dtype=torch.float32, device=tb.device)
+        self.out_depth = torch.empty((h, w), dtype=torch.float32, device=tb.device)
+
+    def set_syn_samples(self, n):
+        self.rt.shadow_iters = n
+
+    def set_nerf_samples(self, n):
+        self.rt.nerf_shadow_kernel = n
+
+    def update_world_objects(self):
+        """≙ Engine::update_world_objects (engine.cu:80-127): advance animations, re-upload the POD arrays."""
+        tb, sc = self.testbed, self.scene
+        sc.advance()
+        tb._check(tb.lib.snb_update_scene(tb.ctx, sc.objects, sc.n_objects, sc.materials, sc.n_materials, sc.lights, sc.n_lights), "snb_update_scene")
+
+    def frame(self, sync=True, host=False):
+        tb = self.testbed
+        v = tb.make_view(self.width, self.height, self.frame_index)
+        tile_ref = C.byref(self.tile) if self.tile is not None else None
+        if host:
+            rgba = np.empty(tuple(self.out_rgba.shape), dtype=np.float32); depth = np.empty(tuple(self.out_depth.shape), dtype=np.float32)
+            tb._check(tb.lib.snb_frame_host(tb.ctx, C.byref(v), tile_ref, C.byref(self.rt), rgba.ctypes.data, depth.ctypes.data), "snb_frame_host")
+            self.frame_index += 1
+            return rgba, depth
+        tb._check(tb.lib.snb_frame(tb.ctx, C.byref(v), tile_ref, C.byref(self.rt), self.out_rgba.data_ptr(), self.out_depth.data_ptr()), "snb_frame")
+        if sync:
+            tb._check(tb.lib.snb_sync(tb.ctx), "snb_sync")
+        self.frame_index += 1
+        return self.out_rgba, self.out_depth

@@ -1,0 +1,67 @@
+"""Shared helpers for the parity tests."""
+import ctypes as C
+import math
+
+import numpy as np
+
+from synerfgine_b200 import _lib
+from synerfgine_b200._lib import View
+from synerfgine_b200.synthetic import SyntheticModel
+
+_models = {}
+
+
+def model(kind="fox16x2"):
+    """Cached synthetic models: the two encodings of SURVEY §0 plus the bounded (aabb 1) and unbounded (aabb 16) cases."""
+    if kind not in _models:
+        cfg = {
+            "fox16x2": dict(n_levels=16, n_feat=2, log2_T=19, aabb_scale=4),
+            "fox8x4": dict(n_levels=8, n_feat=4, log2_T=19, aabb_scale=4),
+            "small16x2": dict(n_levels=16, n_feat=2, log2_T=15, aabb_scale=4),
+            "unit16x2": dict(n_levels=16, n_feat=2, log2_T=15, aabb_scale=1),
+            "big16x2": dict(n_levels=16, n_feat=2, log2_T=16, aabb_scale=16),
+            "f1": dict(n_levels=32, n_feat=1, log2_T=14, aabb_scale=2),
+            "f8": dict(n_levels=4, n_feat=8, log2_T=14, aabb_scale=2),
+            "noocc": dict(n_levels=16, n_feat=2, log2_T=14, aabb_scale=1, occupancy=False, density_gain=12.0),
+        }[kind]
+        _models[kind] = SyntheticModel(**cfg)
+    return _models[kind]
+
+
+def camera_matrix(view=(-0.30, -0.45, -0.84), at=(0.5, 0.42, 0.5), zoom=1.0):
+    lib = _lib.load()
+    out = np.zeros(12, np.float32)
+    v = np.asarray(view, np.float32); a = np.asarray(at, np.float32)
+    assert lib.snb_camera_from_view(v.ctypes.data_as(_lib.pf32), a.ctypes.data_as(_lib.pf32), float(zoom), out.ctypes.data_as(_lib.pf32)) == 0
+    return out
+
+
+def make_view(w, h, cam=None, spp=0, snap=1, fov=50.625):
+    v = View()
+    cam = camera_matrix() if cam is None else cam
+    v.camera[:] = [float(x) for x in cam]
+    f = float(np.float32(0.5 / math.tan(0.5 * fov * math.pi / 180.0)) * np.float32(h))
+    v.focal_length[:] = [f, f]
+    v.screen_center[:] = [0.5, 0.5]
+    v.width, v.height, v.spp, v.snap_to_pixel_centers = w, h, spp, snap
+    return v
+
+
+def psnr(a, b):
+    mse = float(np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2))
+    return 99.0 if mse == 0 else 10.0 * math.log10(1.0 / mse)
+
+
+def default_rt(**kw):
+    """RayTracer / Engine header defaults; keyword overrides."""
+    from synerfgine_b200._lib import RtParams
+    rt = RtParams()
+    rt.n_steps, rt.samples, rt.bounces, rt.shadow_iters = 8, 2, 2, 4
+    rt.lens_angle_constant, rt.depth_offset, rt.syn_shadow_factor = 0.009, 0.1, 1.0
+    rt.view_nerf_shadow, rt.buffer_type, rt.nerf_shadow_kernel = 1, 0, 1
+    rt.nerf_shadow_intensity, rt.nerf_on_nerf_shadow_threshold = 2.0, 0.3
+    rt.show_shadow_on_nerf, rt.show_nerf, rt.syn_px_scale, rt.exposure, rt.tonemap_curve = 1, 1, 1, 0.0, 0
+    for k, v in kw.items():
+        assert hasattr(rt, k), k
+        setattr(rt, k, v)
+    return rt

@@ -1,0 +1,151 @@
+"""GPU parity: NeRF layer of libsnb.so against the CPU oracle (through the C ABI, same seeded inputs).
+
+Bars (BASELINE.json north_star): occupancy traversal sample indices and hash indices bit-exact; framebuffer
+>= 50 dB PSNR and max per-pixel abs error <= 1e-2 for the fp16 MLP output.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def ctx(snb):
+    c = C.c_void_p()
+    assert snb.snb_create(0, None, C.byref(c)) == 0
+    yield c
+    snb.snb_destroy(c)
+
+
+def set_model(snb, ctx, m):
+    d = m.desc()
+    rc = snb.snb_set_model(ctx, C.byref(d))
+    assert rc == 0, snb.snb_last_error(ctx)
+    return d
+
+
+def dev(shape, dtype):
+    return torch.zeros(shape, dtype=dtype, device="cuda")
+
+
+@pytest.mark.parametrize("kind,w,h,spp,snap", [("small16x2", 96, 64, 0, 1), ("small16x2", 64, 48, 3, 0), ("unit16x2", 64, 64, 0, 1), ("big16x2", 64, 64, 1, 0),
+                                                 ("noocc", 32, 32, 0, 1)])
+def test_march_samples_bit_exact(snb, orc, ctx, kind, w, h, spp, snap):
+    m = common.model(kind)
+    d = set_model(snb, ctx, m)
+    cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
+    v = common.make_view(w, h, cam=cam, spp=spp, snap=snap)
+    S = 48
+    n = w * h
+    t, dt, cell, cnt, od = dev((n, S), torch.float32), dev((n, S), torch.float32), dev((n, S), torch.int32), dev((n,), torch.int32), dev((n, 6), torch.float32)
+    assert snb.snb_march_trace(ctx, C.byref(v), S, t.data_ptr(), dt.data_ptr(), cell.data_ptr(), cnt.data_ptr(), od.data_ptr()) == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    rt, rdt, rcell, rcnt, rod = np.zeros((n, S), np.float32), np.zeros((n, S), np.float32), np.zeros((n, S), np.uint32), np.zeros(n, np.uint32), np.zeros((n, 6), np.float32)
+    orc.orc_march_trace(C.byref(d), C.byref(v), S, O.P(rt), O.P(rdt), O.P(rcell, O.pu32), O.P(rcnt, O.pu32), O.P(rod))
+    assert rcnt.sum() > 0, "degenerate test: no samples"
+    np.testing.assert_array_equal(od.cpu().numpy().view(np.uint32), rod.view(np.uint32))          # ray origins / directions
+    np.testing.assert_array_equal(cnt.cpu().numpy().view(np.uint32), rcnt)                         # samples per ray
+    np.testing.assert_array_equal(cell.cpu().numpy().view(np.uint32), rcell)                       # mip << 24 | morton
+    np.testing.assert_array_equal(t.cpu().numpy().view(np.uint32), rt.view(np.uint32))             # t bit pattern
+    np.testing.assert_array_equal(dt.cpu().numpy().view(np.uint32), rdt.view(np.uint32))
+
+
+@pytest.mark.parametrize("kind", ["small16x2", "fox8x4", "f1", "f8", "big16x2"])
+def test_network_hash_indices_and_outputs(snb, orc, ctx, kind):
+    m = common.model(kind)
+    d = set_model(snb, ctx, m)
+    n = 3000 + 7   # ragged: not a multiple of the 32-row tile
+    rng = np.random.default_rng(5)
+    coords = np.zeros((n, 7), np.float32)
+    coords[:, :3] = rng.uniform(0.0, 1.0, (n, 3)); coords[:, 3] = 0.01; coords[:, 4:] = rng.uniform(0.0, 1.0, (n, 3))
+    coords[0, :3] = 0.0; coords[1, :3] = 1.0    # box corners
+    L = m.n_levels
+    dc = torch.from_numpy(coords).cuda()
+    out, feat, hidx = dev((n, 4), torch.float16), dev((n, 32), torch.float16), dev((n, L * 8), torch.int32)
+    assert snb.snb_network_inference(ctx, dc.data_ptr(), n, out.data_ptr(), feat.data_ptr(), hidx.data_ptr()) == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    rout, rfeat, rh = np.zeros((n, 4), np.uint16), np.zeros((n, 32), np.uint16), np.zeros((n, L * 8), np.uint32)
+    orc.orc_network_inference(C.byref(d), O.P(coords), n, O.P(rout, O.pu16), O.P(rfeat, O.pu16), O.P(rh, O.pu32))
+    np.testing.assert_array_equal(hidx.cpu().numpy().view(np.uint32), rh)                                   # hash indices: bit-exact
+    np.testing.assert_array_equal(feat.cpu().numpy().view(np.uint16), rfeat)                                # fp16 features: same fma order -> bit-exact
+    a = out.cpu().numpy().astype(np.float32); b = rout.view(np.float16).astype(np.float32)
+    # MLP: tensor-core fp32 accumulation order differs from the scalar oracle -> compare within fp16 rounding of the outputs
+    tol = 2e-3 * np.maximum(1.0, np.abs(b)) * 4
+    assert np.all(np.abs(a - b) <= tol), f"max |diff| {np.abs(a - b).max()}"
+    assert np.abs(b).max() > 0.1
+
+
+@pytest.mark.parametrize("kind,alt,w,h", [("small16x2", 0, 128, 96), ("small16x2", 1, 128, 96), ("fox8x4", 1, 64, 64), ("unit16x2", 0, 64, 64), ("big16x2", 1, 64, 64)])
+def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h):
+    m = common.model(kind)
+    d = set_model(snb, ctx, m)
+    cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
+    v = common.make_view(w, h, cam=cam)
+    fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    rt = common.default_rt(show_shadow_on_nerf=0)
+    if alt:
+        pos, nrm = dev((h, w, 3), torch.float32), dev((h, w, 3), torch.float32)
+        rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(), pos.data_ptr(), nrm.data_ptr())
+    else:
+        rc = snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr())
+    assert rc == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    rfb, rdepth, rpos, ns = O.render_nerf(d, v, alt, positions=bool(alt))
+    a = fb.cpu().numpy()
+    assert (rfb[..., 3] > 0.5).mean() > 0.1, "degenerate test: nothing visible"
+    err = np.abs(a - rfb)
+    assert common.psnr(a, rfb) >= 50.0, common.psnr(a, rfb)
+    assert err.max() <= 1e-2, err.max()
+    # depth: same samples -> agree wherever both wrote it; allow the rare ray whose termination step differs by one sample
+    dd = np.abs(depth.cpu().numpy() - rdepth)
+    assert (dd > 0.05).mean() < 2e-3, (dd > 0.05).mean()
+    cnt = (C.c_uint64 * 4)()
+    assert snb.snb_get_counters(ctx, cnt) == 0
+    assert abs(int(cnt[0]) - int(ns)) <= 0.002 * ns + 8, (cnt[0], ns)       # network samples evaluated
+    if alt:
+        pd = np.abs(pos.cpu().numpy() - rpos)
+        assert (pd.max(-1) > 0.05).mean() < 2e-3
+        rn = np.zeros((h * w, 3), np.float32)
+        gp = pos.cpu().numpy().reshape(-1, 3).copy()
+        orc.orc_write_normals(w, h, O.P(gp), O.P(rn))                          # normals from the product's own positions: exact stencil parity
+        np.testing.assert_allclose(nrm.cpu().numpy().reshape(-1, 3), rn, atol=1e-6)
+
+
+def test_tile_equals_crop_of_full_frame(snb, ctx):
+    from synerfgine_b200._lib import Tile
+    m = common.model("small16x2")
+    set_model(snb, ctx, m)
+    w, h = 96, 64
+    v = common.make_view(w, h, spp=2, snap=0)
+    full, fdepth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, full.data_ptr(), fdepth.data_ptr()) == 0
+    t = Tile(40, 16, 48, 32)
+    part, pdepth = dev((t.h, t.w, 4), torch.float32), dev((t.h, t.w), torch.float32)
+    assert snb.snb_render_nerf(ctx, C.byref(v), C.byref(t), 1, part.data_ptr(), pdepth.data_ptr()) == 0
+    assert snb.snb_sync(ctx) == 0
+    assert torch.equal(part, full[t.y0:t.y0 + t.h, t.x0:t.x0 + t.w])
+    assert torch.equal(pdepth, fdepth[t.y0:t.y0 + t.h, t.x0:t.x0 + t.w])
+
+
+def test_bitfield_builder_matches_host_twin(snb, ctx):
+    from synerfgine_b200 import synthetic
+    m = common.model("small16x2")
+    out = np.zeros(synthetic.CASCADES * synthetic.CELLS // 8, np.uint8)
+    dens = np.ascontiguousarray(m.density)
+    assert snb.snb_density_to_bitfield(ctx, dens.ctypes.data_as(C.POINTER(C.c_float)), m.max_cascade, out.ctypes.data_as(C.POINTER(C.c_uint8))) == 0
+    np.testing.assert_array_equal(out, m.bitfield)
+
+
+def test_errors_are_reported_not_thrown(snb, ctx):
+    v = common.make_view(16, 16)
+    assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, None, None) != 0
+    from synerfgine_b200._lib import ModelDesc
+    bad = common.model("small16x2").desc(); bad.n_levels = 5
+    assert snb.snb_set_model(ctx, C.byref(bad)) != 0
+    assert b"n_levels" in snb.snb_last_error(ctx)
