@@ -9,7 +9,10 @@ from .synthetic import SyntheticModel  # noqa: F401
 
 
 def __getattr__(name):  # torch-dependent classes are imported on first use
-    if name in ("Testbed", "Engine", "Scene"):
+    if name == "Scene":
+        from .scene import Scene
+        return Scene
+    if name in ("Testbed", "Engine"):
         from . import testbed
         return getattr(testbed, name)
     raise AttributeError(name)

@@ -79,6 +79,7 @@ SIGNATURES = {
     "snb_network_inference": (C.c_int, [vp, vp, u64, vp, vp, vp]),
     "snb_trace_rays": (C.c_int, [vp, vp, u32, vp, vp, vp]),
     "snb_get_counters": (C.c_int, [vp, C.POINTER(u64)]),
+    "snb_get_stage_ms": (C.c_int, [vp, pf32]),
     "snb_launch_count": (u64, [vp]),
     "snb_scene_load_json": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),
     "snb_scene_free": (None, [vp]),

@@ -65,6 +65,13 @@ struct snb_ctx {
 	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
 
+	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)
+	static const int kStages = 5;   // 0 nerf raygen, 1 nerf fused march, 2 nerf normals+shadows, 3 mesh layer, 4 overlay
+	cudaEvent_t ev[kStages][2] = {};
+	bool ev_set[kStages] = {};
+	void stage_begin(int s) { if (!ev[s][0]) { cudaEventCreate(&ev[s][0]); cudaEventCreate(&ev[s][1]); } cudaEventRecord(ev[s][0], stream); ev_set[s] = false; }
+	void stage_end(int s) { cudaEventRecord(ev[s][1], stream); ev_set[s] = true; }
+
 	int fail(int code, const std::string& msg) { err = msg; return code; }
 	int cuda_fail(cudaError_t e, const char* what) {
 		char buf[256]; snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));

@@ -42,12 +42,21 @@ SNB_HD Stepping make_stepping(float cone) {
 	return s;
 }
 
+// Coarse look-ahead grid: kCoarseRes^3 bits over the extent of cascade max_mip, a dilated superset of every occupied
+// cell of cascades 0..max_mip (built once per model by k_build_coarse). It never changes a march result: it only proves
+// "no occupied cell ahead", in which case the DDA would have walked to the edge of the render box and returned kMaxDepth.
+constexpr int kCoarseRes = 32;
+constexpr int kCoarseWords = kCoarseRes * kCoarseRes * kCoarseRes / 32;   // 1024 words = 4 KB (staged in shared memory)
+
 struct MarchEnv {
 	const uint8_t* bitfield;   // kCascades * 128^3 / 8 bytes, Morton order per cascade; nullptr = all occupied
 	uint32_t min_mip, max_mip;
 	Aabb render_aabb;
 	m3 to_local;               // render_aabb_to_local
 	Stepping st;
+	const uint32_t* coarse;    // kCoarseWords words or nullptr (no look-ahead)
+	v3 coarse_lo;              // world position of coarse cell (0,0,0)
+	float coarse_inv_cell;     // coarse cells per world unit
 };
 
 SNB_HD uint32_t spread3(uint32_t v) { // tcnn/common_device.h:761-770

@@ -46,8 +46,11 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches = ((dv.tw + 7) / 8) * ((dv.th + 3) / 4);
+	c->stage_begin(0);
 	k_nerf_raygen<<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, c->d_queue.as<RayRec>(), qctl);
 	SNB_LAUNCHED(c);
+	c->stage_end(0);
+	c->stage_begin(1);
 	int rc;
 	switch (c->feat_per_level) {
 		case 1: rc = alt ? launch_fused<1, true>(c, dv, out, render_mode, n_px) : launch_fused<1, false>(c, dv, out, render_mode, n_px); break;
@@ -55,6 +58,7 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 		case 4: rc = alt ? launch_fused<4, true>(c, dv, out, render_mode, n_px) : launch_fused<4, false>(c, dv, out, render_mode, n_px); break;
 		default: rc = alt ? launch_fused<8, true>(c, dv, out, render_mode, n_px) : launch_fused<8, false>(c, dv, out, render_mode, n_px); break;
 	}
+	c->stage_end(1);
 	return rc;
 }
 
@@ -94,6 +98,7 @@ static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* 
 	SNB_CUDA(c, c->d_syn_rgba.reserve((size_t)n * 16));
 	SNB_CUDA(c, c->d_syn_depth.reserve((size_t)n * 4));
 	const dim3 grid2((dv.tw + 15) / 16, (dv.th + 7) / 8);
+	c->stage_begin(3);
 	if (c->syn_reset) {
 		k_syn_raygen<<<grid2, 128, 0, c->stream>>>(dv, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), nullptr, nullptr, c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
 		SNB_LAUNCHED(c);
@@ -102,12 +107,14 @@ static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* 
 	k_raytrace<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
 	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
 	SNB_LAUNCHED(c);
+	c->stage_end(3);
 	return SNB_OK;
 }
 
 // Normals + mesh shadows on the NeRF layer (tile-sized buffers; window reads stop at the tile edge like at the image edge).
 static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int render_mode, float* fb, float* positions, float* normals) {
 	const dim3 grid2((dv.tw + 15) / 16, (dv.th + 7) / 8);
+	c->stage_begin(2);
 	k_write_normals<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, positions, normals);
 	SNB_LAUNCHED(c);
 	if (rt->show_shadow_on_nerf) {
@@ -121,6 +128,7 @@ static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int
 		                                                  reinterpret_cast<float4*>(fb), nullptr);
 		SNB_LAUNCHED(c);
 	}
+	c->stage_end(2);
 	return SNB_OK;
 }
 
@@ -179,10 +187,12 @@ int snb_overlay(snb_ctx* c, int syn_w, int syn_h, const snb_rt_params* rt, const
 	if (!c || !rt || !syn_rgba || !syn_depth || !nerf_rgba || !nerf_depth || !out_rgba || syn_w <= 0 || syn_h <= 0) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));
 	const dim3 grid2((syn_w + 15) / 16, (syn_h + 7) / 8);
+	c->stage_begin(4);
 	k_overlay<<<grid2, 128, 0, c->stream>>>(syn_w, syn_h, std::max(1, rt->syn_px_scale), reinterpret_cast<const float4*>(syn_rgba), syn_depth,
 	                                        reinterpret_cast<const float4*>(nerf_rgba), nerf_depth, rt->show_nerf, 1, rt->tonemap_curve, rt->exposure, rt->depth_offset,
 	                                        reinterpret_cast<float4*>(out_rgba), out_depth);
 	SNB_LAUNCHED(c);
+	c->stage_end(4);
 	return SNB_OK;
 }
 

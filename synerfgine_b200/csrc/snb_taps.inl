@@ -85,6 +85,17 @@ int snb_get_counters(snb_ctx* c, uint64_t* out4) {
 	return SNB_OK;
 }
 
+int snb_get_stage_ms(snb_ctx* c, float* out5) {
+	if (!c || !out5) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	for (int s = 0; s < snb_ctx::kStages; ++s) {
+		out5[s] = 0.0f;
+		if (c->ev_set[s]) cudaEventElapsedTime(&out5[s], c->ev[s][0], c->ev[s][1]);
+	}
+	return SNB_OK;
+}
+
 int snb_density_to_bitfield(snb_ctx* c, const float* density_host, uint32_t max_cascade, uint8_t* bitfield_out_host) {
 	if (!c || !density_host || !bitfield_out_host || max_cascade >= kCascades) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));

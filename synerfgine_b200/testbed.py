@@ -11,7 +11,8 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import Light, Material, Object, RtParams, Tile, View
+from ._lib import RtParams, Tile, View  # noqa: F401
+from .scene import Scene  # noqa: F401
 
 
 def _fp(a):
@@ -21,14 +22,16 @@ def _fp(a):
 class Testbed:
     """NeRF-only render entry: ``render(width, height, spp, linear)`` -> float32 [H, W, 4] like pyngp.Testbed.render."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, stream=None):
+        """stream: optional torch.cuda.Stream the context enqueues on (so torch events can time it); default: own stream."""
         if not torch.cuda.is_available():
             raise RuntimeError("synerfgine_b200 needs a CUDA device (no CPU fallback)")
         self.lib = _lib.load()
         self.device = torch.device("cuda", device)
         torch.cuda.set_device(self.device)
         self.ctx = C.c_void_p()
-        rc = self.lib.snb_create(device, None, C.byref(self.ctx))
+        self.stream = stream
+        rc = self.lib.snb_create(device, C.c_void_p(stream.cuda_stream) if stream is not None else None, C.byref(self.ctx))
         if rc != 0:
             raise _lib.SnbError(f"snb_create failed ({rc})")
         # Testbed::reset_camera defaults (src/testbed.cu:470-492)
@@ -129,56 +132,14 @@ class Testbed:
         self._check(self.lib.snb_get_counters(self.ctx, out), "snb_get_counters")
         return {"samples": out[0], "rays": out[1], "hits": out[2]}
 
+    def stage_ms(self):
+        """Device time of the last frame's stages (synchronises): nerf_raygen, nerf_march, nerf_post, mesh, overlay."""
+        out = (C.c_float * 5)()
+        self._check(self.lib.snb_get_stage_ms(self.ctx, out), "snb_get_stage_ms")
+        return dict(zip(("nerf_raygen", "nerf_march", "nerf_post", "mesh", "overlay"), [float(x) for x in out]))
+
     def launch_count(self):
         return int(self.lib.snb_launch_count(self.ctx))
-
-
-class Scene:
-    """Parsed virtual-scene JSON (host side): objects with BVHs, materials, lights, rendering settings, camera path."""
-
-    def __init__(self, json_text, base_dir=None):
-        self.lib = _lib.load()
-        self.handle = C.c_void_p()
-        err = C.create_string_buffer(512)
-        rc = self.lib.snb_scene_load_json(json_text.encode(), base_dir.encode() if base_dir else None, C.byref(self.handle), err, 512)
-        if rc != 0:
-            raise _lib.SnbError(f"scene JSON: {err.value.decode()}")
-        self.refresh()
-        view = (C.c_float * 3)(); at = (C.c_float * 3)(); zoom = C.c_float(); vo = C.c_float(); nk = C.c_uint32()
-        self.lib.snb_scene_camera(self.handle, view, at, C.byref(zoom), C.byref(vo), C.byref(nk))
-        self.view_dir, self.at_pos, self.zoom, self.vo_scale, self.n_keyframes = list(view), list(at), zoom.value, vo.value, nk.value
-
-    @classmethod
-    def from_file(cls, path, base_dir=None):
-        with open(path) as f:
-            return cls(f.read(), base_dir if base_dir is not None else os.path.dirname(os.path.abspath(path)))
-
-    def refresh(self):
-        no, nm, nl = C.c_uint32(), C.c_uint32(), C.c_uint32()
-        self.lib.snb_scene_counts(self.handle, C.byref(no), C.byref(nm), C.byref(nl))
-        self.objects = (Object * max(1, no.value))(); self.materials = (Material * max(1, nm.value))(); self.lights = (Light * max(1, nl.value))()
-        self.n_objects, self.n_materials, self.n_lights = no.value, nm.value, nl.value
-        self.rt = RtParams()
-        self.lib.snb_scene_get(self.handle, self.objects, self.materials, self.lights, C.byref(self.rt))
-
-    def camera_at(self, frame, total_frames=0):
-        view = (C.c_float * 3)(); at = (C.c_float * 3)(); zoom = C.c_float()
-        rc = self.lib.snb_scene_camera_at(self.handle, frame, total_frames, view, at, C.byref(zoom))
-        if rc != 0:
-            raise _lib.SnbError("scene has no camera path")
-        return list(view), list(at), zoom.value
-
-    def advance(self):
-        self.lib.snb_scene_advance(self.handle)
-        self.refresh()
-
-    def __del__(self):
-        try:
-            if self.handle:
-                self.lib.snb_scene_free(self.handle)
-                self.handle = C.c_void_p()
-        except Exception:
-            pass
 
 
 class Engine:
