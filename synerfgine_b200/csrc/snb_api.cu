@@ -64,7 +64,7 @@ void snb_destroy(snb_ctx* c) {
 	if (!c) return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
-	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
+	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_coarse, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
 	                  &c->d_counters, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
@@ -121,6 +121,20 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	d.env.render_aabb.lo = ld3(m->render_aabb_min); d.env.render_aabb.hi = ld3(m->render_aabb_max);
 	d.env.to_local = ldm3(m->render_aabb_to_local);
 	d.env.st = make_stepping(m->cone_angle_constant);
+	// coarse look-ahead grid over the extent of cascade max_cascade (snb_march.cuh)
+	d.env.coarse = nullptr;
+	const float extent = std::ldexp(1.0f, (int)m->max_cascade);
+	d.env.coarse_lo = mk3(0.5f - 0.5f * extent, 0.5f - 0.5f * extent, 0.5f - 0.5f * extent);
+	d.env.coarse_inv_cell = (float)kCoarseRes / extent;
+	if (m->bitfield) {
+		SNB_CUDA(c, c->d_coarse.reserve(kCoarseWords * 4));
+		SNB_CUDA(c, cudaMemsetAsync(c->d_coarse.p, 0, kCoarseWords * 4, c->stream));
+		const uint32_t n_bytes = kGridCells / 8 * (m->max_cascade + 1);
+		k_build_coarse<<<(n_bytes + 127) / 128, 128, 0, c->stream>>>(c->d_bitfield.as<uint8_t>(), n_bytes, d.env.coarse_lo, d.env.coarse_inv_cell, c->d_coarse.as<uint32_t>());
+		SNB_LAUNCHED(c);
+		SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+		d.env.coarse = c->d_coarse.as<uint32_t>();
+	}
 	c->feat_per_level = F;
 	c->has_model = true;
 	return SNB_OK;

@@ -136,14 +136,44 @@ SNB_HD uint32_t clamp_mip(uint32_t mip, const MarchEnv& env) {
 	return mip;
 }
 
+// Conservative "is anything occupied ahead of pos along d?" — a 3-D DDA through the coarse grid. Returns true when
+// every coarse cell the ray touches from pos to the edge of the coarse domain is empty. Positions outside the domain
+// (or a missing grid) answer false, i.e. "cannot tell".
+SNB_HD bool coarse_clear_ahead(v3 pos, v3 d, const MarchEnv& env) {
+	if (!env.coarse) return false;
+	const float R = (float)kCoarseRes;
+	const v3 g = (pos - env.coarse_lo) * env.coarse_inv_cell;
+	if (!(g.x >= 0.0f && g.x < R && g.y >= 0.0f && g.y < R && g.z >= 0.0f && g.z < R)) return false;
+	int ix = (int)g.x, iy = (int)g.y, iz = (int)g.z;
+	const int sx = d.x > 0.0f ? 1 : -1, sy = d.y > 0.0f ? 1 : -1, sz = d.z > 0.0f ? 1 : -1;
+	const float big = 3.0e38f;
+	const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+	const float dx = ax > 1e-12f ? 1.0f / ax : big, dy = ay > 1e-12f ? 1.0f / ay : big, dz = az > 1e-12f ? 1.0f / az : big;   // grid units of t per cell
+	float tx = ax > 1e-12f ? (sx > 0 ? ((float)(ix + 1) - g.x) : (g.x - (float)ix)) * dx : big;
+	float ty = ay > 1e-12f ? (sy > 0 ? ((float)(iy + 1) - g.y) : (g.y - (float)iy)) * dy : big;
+	float tz = az > 1e-12f ? (sz > 0 ? ((float)(iz + 1) - g.z) : (g.z - (float)iz)) * dz : big;
+	for (int guard = 0; guard < 3 * kCoarseRes + 3; ++guard) {
+		const uint32_t bit = (uint32_t)ix + (uint32_t)kCoarseRes * ((uint32_t)iy + (uint32_t)kCoarseRes * (uint32_t)iz);
+		if (env.coarse[bit >> 5] & (1u << (bit & 31))) return false;
+		if (tx <= ty && tx <= tz) { ix += sx; tx += dx; if ((unsigned)ix >= (unsigned)kCoarseRes) return true; }
+		else if (ty <= tz) { iy += sy; ty += dy; if ((unsigned)iy >= (unsigned)kCoarseRes) return true; }
+		else { iz += sz; tz += dz; if ((unsigned)iz >= (unsigned)kCoarseRes) return true; }
+	}
+	return false;
+}
+
 // Skip empty space: returns the first t >= t_in whose enclosing cascade cell is occupied, or kMaxDepth
-// once the ray leaves the render box.
+// once the ray leaves the render box. Every kLookAheadEvery-th empty cell the coarse grid is consulted: if nothing
+// can be occupied ahead, the remaining DDA steps (which could only end in kMaxDepth) are not walked.
+constexpr int kLookAheadEvery = 8;
 SNB_HD float skip_to_occupied(float t, v3 o, v3 d, v3 idir, const MarchEnv& env) {
+	int n_empty = 0;
 	while (true) {
 		const v3 pos = o + d * t;
 		if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) return kMaxDepth;
 		uint32_t mip = clamp_mip(mip_of(pos), env);
 		if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) return t;
+		if ((n_empty++ % kLookAheadEvery) == 0 && coarse_clear_ahead(pos, d, env)) return kMaxDepth;
 		while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
 		t = advance_past_voxel(t, env.st, pos, d, idir, mip);
 	}

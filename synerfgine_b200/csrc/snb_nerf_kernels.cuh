@@ -56,6 +56,39 @@ SNB_D int tile_local_index(const DevView& v, uint32_t gidx) {
 	return x + v.tw * y;
 }
 
+// ---- coarse look-ahead grid (once per model) ------------------------------------------------------------------------
+// One thread per bitfield byte of cascades 0..max_mip; every set bit marks the coarse cells its world box touches,
+// dilated by one coarse cell so that a DDA grazing a cell corner can never miss it.
+__global__ void __launch_bounds__(128) k_build_coarse(const uint8_t* __restrict__ bitfield, uint32_t n_bytes, v3 coarse_lo, float inv_cell, uint32_t* __restrict__ coarse) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_bytes) return;
+	const uint8_t byte = bitfield[i];
+	if (!byte) return;
+	const uint32_t mip = i / (kGridCells / 8);
+	const float cell = scalbnf(1.0f / (float)kGridSize, (int)mip), half = scalbnf(0.5f, (int)mip);
+	for (int j = 0; j < 8; ++j) {
+		if (!(byte & (1u << j))) continue;
+		const uint32_t m = (i % (kGridCells / 8)) * 8 + j;
+		uint32_t xyz[3];
+		for (int a = 0; a < 3; ++a) {
+			uint32_t x = (m >> a) & 0x49249249u;
+			x = (x | (x >> 2)) & 0xc30c30c3u; x = (x | (x >> 4)) & 0x0f00f00fu; x = (x | (x >> 8)) & 0xff0000ffu; x = (x | (x >> 16)) & 0x0000ffffu;
+			xyz[a] = x;
+		}
+		int lo[3], hi[3];
+		const float base[3] = {coarse_lo.x, coarse_lo.y, coarse_lo.z};
+		for (int a = 0; a < 3; ++a) {
+			const float wlo = (float)xyz[a] * cell - half + 0.5f, whi = wlo + cell;
+			lo[a] = max(0, (int)floorf((wlo - base[a]) * inv_cell) - 1);
+			hi[a] = min(kCoarseRes - 1, (int)floorf((whi - base[a]) * inv_cell) + 1);
+		}
+		for (int z = lo[2]; z <= hi[2]; ++z) for (int y = lo[1]; y <= hi[1]; ++y) for (int x = lo[0]; x <= hi[0]; ++x) {
+			const uint32_t bit = (uint32_t)x + (uint32_t)kCoarseRes * ((uint32_t)y + (uint32_t)kCoarseRes * (uint32_t)z);
+			atomicOr(&coarse[bit >> 5], 1u << (bit & 31));
+		}
+	}
+}
+
 // ---- ray generation: one thread per tile pixel, 8x4 pixel patches per warp so queue neighbours are image neighbours ----
 __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail) {
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -121,6 +154,8 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	__shared__ __align__(16) uint32_t s_w[kFragWords];
 	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
 	__shared__ GridDesc s_grid;   // level scales / resolutions / offsets staged once per CTA
+	__shared__ uint32_t s_coarse[kCoarseWords];   // look-ahead occupancy (4 KB)
+	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += kFusedThreads) s_coarse[i] = __ldg(model.env.coarse + i);
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
 	for (int i = threadIdx.x; i < (int)(sizeof(GridDesc) / 4); i += kFusedThreads)
@@ -131,7 +166,8 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
 	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
 	const unsigned int n_rays = *queue_tail;
-	const MarchEnv& env = model.env;
+	MarchEnv env = model.env;
+	if (env.coarse) env.coarse = s_coarse;
 	const v3 cam_fwd = view.cam.c2;
 	const v3 aabb_diag = model.train_aabb.diag();
 
