@@ -68,8 +68,12 @@ SNB_HD uint32_t spread3(uint32_t v) { // tcnn/common_device.h:761-770
 }
 SNB_HD uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) { return spread3(x) | (spread3(y) << 1) | (spread3(z) << 2); }
 
+// 2^e for small |e| as an exponent-field constant: x * pow2i(e) == scalbnf(x, e) whenever neither under- nor overflows,
+// which holds for every use below (|e| <= 8, operands of order 1).
+SNB_HD float pow2i(int e) { return u2f((uint32_t)(127 + e) << 23); }
+
 SNB_HD uint32_t cascade_cell(v3 pos, uint32_t mip) {
-	const float mip_scale = scalbnf(1.0f, -(int)mip);
+	const float mip_scale = pow2i(-(int)mip);
 	pos = pos - 0.5f;
 	pos = pos * mip_scale;
 	pos = pos + 0.5f;
@@ -89,13 +93,13 @@ SNB_HD bool cell_occupied(v3 pos, const uint8_t* bitfield, uint32_t mip) {
 	return byte & (1u << (idx % 8));
 }
 
-SNB_HD float voxel_exit_distance(v3 pos, v3 dir, v3 idir, float res) {
+SNB_HD float voxel_exit_distance(v3 pos, v3 dir, v3 idir, float res, float inv_res) {
 	const v3 p = res * (pos - 0.5f);
 	const float tx = (floorf(p.x + 0.5f + 0.5f * copysignf(1.0f, dir.x)) - p.x) * idir.x;
 	const float ty = (floorf(p.y + 0.5f + 0.5f * copysignf(1.0f, dir.y)) - p.y) * idir.y;
 	const float tz = (floorf(p.z + 0.5f + 0.5f * copysignf(1.0f, dir.z)) - p.z) * idir.z;
 	const float t = fminf(fminf(tx, ty), tz);
-	return fmaxf(t / res, 0.0f);
+	return fmaxf(t * inv_res, 0.0f);   // res is a power of two: t / res == t * (1 / res) exactly
 }
 
 SNB_HD float to_step_space(float t, const Stepping& s) {
@@ -114,17 +118,17 @@ SNB_HD float advance_steps(float t, const Stepping& s, float n) { return from_st
 SNB_HD float step_size(float t, const Stepping& s) { return advance_steps(t, s, 1.0f) - t; }
 
 SNB_HD float advance_past_voxel(float t, const Stepping& s, v3 pos, v3 dir, v3 idir, uint32_t mip) {
-	const float res = scalbnf((float)kGridSize, -(int)mip);
-	float t_target = t + voxel_exit_distance(pos, dir, idir, res);
+	const float res = (float)kGridSize * pow2i(-(int)mip), inv_res = pow2i((int)mip) * (1.0f / (float)kGridSize);
+	float t_target = t + voxel_exit_distance(pos, dir, idir, res, inv_res);
 	t = to_step_space(t, s);
 	t_target = to_step_space(t_target, s);
 	return from_step_space(t + ceilf(fmaxf(t_target - t, 0.5f)), s);
 }
 
 SNB_HD uint32_t mip_of(v3 pos, uint32_t max_cascade = kCascades - 1) {
-	int exponent;
+	// frexpf exponent from the exponent field; zero / subnormal inputs give a negative m either way and clamp to 0
 	const float maxval = vmax(vabs(pos - 0.5f));
-	frexpf(maxval, &exponent);
+	const int exponent = (int)((f2u(maxval) >> 23) & 0xFFu) - 126;
 	int m = exponent + 1;
 	if (m < 0) m = 0;
 	if (m > (int)max_cascade) m = (int)max_cascade;

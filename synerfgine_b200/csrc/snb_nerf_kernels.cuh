@@ -31,13 +31,13 @@ struct NerfOut {                     // tile-sized output buffers
 	float* positions;                // xyz per pixel (alt path) or nullptr
 };
 
-SNB_D float act_logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
+SNB_D float act_logistic(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 SNB_D float act_rgb(float v, int act) {
 	switch (act) {
 		case 0: return v;
 		case 1: return v > 0.0f ? v : 0.0f;
 		case 2: return act_logistic(v);
-		default: return expf(fminf(fmaxf(v, -10.0f), 10.0f));
+		default: return __expf(fminf(fmaxf(v, -10.0f), 10.0f));
 	}
 }
 SNB_D float act_density(float v, int act) {
@@ -45,7 +45,7 @@ SNB_D float act_density(float v, int act) {
 		case 0: return v;
 		case 1: return v > 0.0f ? v : 0.0f;
 		case 2: return act_logistic(v);
-		default: return expf(v);
+		default: return __expf(v);
 	}
 }
 SNB_HD float dt_warp(float dt) { const float mx = kMinStep * (1 << 7); return (dt - kMinStep) / (mx - kMinStep); }
@@ -127,8 +127,9 @@ __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env,
 	}
 }
 
-// Finished ray -> pixel (extract_from_payload for the sng path, shade_kernel_nerf for the stock path).
-SNB_D void write_pixel(const DevView& view, const NerfOut& out, bool alt, int render_mode, uint32_t idx, v3 dir, float t, float4 rgba, float depth) {
+// Finished ray -> pixel (extract_from_payload for the sng path, shade_kernel_nerf for the stock path). Runs once per
+// ray, so it is kept out of line: the march loop has to stay small (instruction cache).
+__device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out, bool alt, int render_mode, uint32_t idx, v3 dir, float t, float4 rgba, float depth) {
 	const int l = tile_local_index(view, idx);
 	float4 tmp = rgba;
 	if (alt) {
@@ -146,20 +147,25 @@ SNB_D void write_pixel(const DevView& view, const NerfOut& out, bool alt, int re
 
 // ---- the persistent fused kernel -----------------------------------------------------------------------------------
 // grid = SMs x resident CTAs, block = 4 warps; smem = fragment-ordered MLP weights (20 KB, shared by the CTA) +
-// per-warp staging tile (3.5 KB) + per-warp output tile (256 B).
+// per-warp staging tile (3.5 KB) + per-warp output tile (256 B) + level table (1 KB) + look-ahead grid (4 KB).
+//
+// One loop iteration of a warp = (1) refill finished slots from the queue, (2) search phase: lanes whose ray sits in
+// empty space take DDA steps until at least kMinFill lanes hold a sample position (lanes that already have one
+// wait), (3) encode + both MLPs for the lanes that have a sample, (4) composite. A lane still searching after (2)
+// simply carries on in the next iteration, so one ray crossing a long empty gap no longer stalls the other 31.
+constexpr int kMinFill = 26;
 template <int F, bool ALT>
-__global__ void __launch_bounds__(kFusedThreads, 3)
+__global__ void __launch_bounds__(kFusedThreads, 4)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
                    unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
 	__shared__ __align__(16) uint32_t s_w[kFragWords];
 	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
-	__shared__ GridDesc s_grid;   // level scales / resolutions / offsets staged once per CTA
+	__shared__ LevelDesc s_levels[kMaxLevels];
 	__shared__ uint32_t s_coarse[kCoarseWords];   // look-ahead occupancy (4 KB)
 	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += kFusedThreads) s_coarse[i] = __ldg(model.env.coarse + i);
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
-	for (int i = threadIdx.x; i < (int)(sizeof(GridDesc) / 4); i += kFusedThreads)
-		reinterpret_cast<uint32_t*>(&s_grid)[i] = reinterpret_cast<const uint32_t*>(&model.grid)[i];
+	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x);
 	__syncthreads();
 
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -173,21 +179,23 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 
 	// per-slot ray state
 	v3 o = mk3(0, 0, 0), d = mk3(1, 0, 0), idir = mk3(1, 1, 1);
-	float t = 0.0f, depth = 0.0f, max_weight = 0.0f;
+	float t = 0.0f, depth = 0.0f;
 	float4 rgba = make_float4(0, 0, 0, 0);
 	uint32_t idx = 0, step_i = 1;
-	int k = 0;
+	int k = 0, n_empty = 0;
 	bool alive = false, drained = false;
+	float max_weight = 0.0f;
 	uint32_t sh_frag[2][4];
 #pragma unroll
 	for (int m = 0; m < 2; ++m)
 #pragma unroll
 		for (int i = 0; i < 4; ++i) sh_frag[m][i] = 0u;
-	{ // zero the SH block once so never-filled rows hold finite values
-		const uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-		stage_sh_row(tile, lane, z);
+	{ // zero the whole row once so never-filled rows hold finite values
+		uint4* row = reinterpret_cast<uint4*>(tile + lane * kTileStrideH);
+#pragma unroll
+		for (int i = 0; i < kTileStrideH * 2 / 16; ++i) row[i] = make_uint4(0, 0, 0, 0);
 	}
-	unsigned long long n_samples = 0, n_hits = 0, n_launched = 0;
+	uint32_t n_samples = 0, n_hits = 0, n_launched = 0;
 
 	auto finish = [&]() {
 		alive = false;
@@ -209,7 +217,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				const float4 q1 = __ldg(reinterpret_cast<const float4*>(queue + mine) + 1);
 				o = mk3(q0.x, q0.y, q0.z); t = q0.w; d = mk3(q1.x, q1.y, q1.z); idx = __float_as_uint(q1.w);
 				idir = 1.0f / d;
-				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; alive = true;
+				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; n_empty = 0; alive = true;
 				++n_launched;
 				uint32_t sh[8];
 				encode_direction_sh4((d + 1.0f) * 0.5f, sh);   // warp_direction, nerf_device.cuh:290-292
@@ -221,29 +229,44 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		}
 		if (__ballot_sync(0xFFFFFFFFu, alive) == 0) break;
 
-		// -- one march step per live slot ----------------------------------------------------------------------------
+		// -- search phase: the skip loop of if_unoccupied_advance_to_next_occupied_voxel, one DDA step per pass -----------
 		bool valid = false;
-		v3 wpos = mk3(0, 0, 0);
-		float wdt = 0.0f;
-		if (alive) {
-			t = skip_to_occupied(t, o, d, idir, env);
-			if (t >= kMaxDepth) {
-				finish();                                        // left the volume: batch ends short, ray is done
-			} else {
-				const float dt = step_size(t, env.st);
-				wpos = (o + d * t - model.train_aabb.lo) / aabb_diag;   // warp_position
-				wdt = dt_warp(dt);
-				t += dt;
-				valid = true;
+		{
+			bool searching = alive;
+#pragma unroll 1
+			for (;;) {
+				if (searching) {
+					const v3 pos = o + d * t;
+					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { finish(); searching = false; }   // left the volume
+					else {
+						uint32_t mip = clamp_mip(mip_of(pos), env);
+						if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) { valid = true; searching = false; n_empty = 0; }
+						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { finish(); searching = false; }
+						else {
+							while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
+							t = advance_past_voxel(t, env.st, pos, d, idir, mip);
+						}
+					}
+				}
+				if (__ballot_sync(0xFFFFFFFFu, searching) == 0) break;
+				if (__popc(__ballot_sync(0xFFFFFFFFu, valid)) >= kMinFill) break;
 			}
 		}
+		if (__ballot_sync(0xFFFFFFFFu, valid) == 0) continue;
 
-		// -- network: gather + both MLPs -------------------------------------------------------------------------------
-		uint32_t feat[16];
-#pragma unroll
-		for (int i = 0; i < 16; ++i) feat[i] = 0u;
-		if (valid) encode_position<F>(s_grid, model.grid_params, wpos, feat, nullptr);
-		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, feat, sh_frag);
+		// -- sample position -------------------------------------------------------------------------------------------
+		v3 wpos = mk3(0, 0, 0);
+		float wdt = 0.0f;
+		if (valid) {
+			const float dt = step_size(t, env.st);
+			wpos = (o + d * t - model.train_aabb.lo) / aabb_diag;   // warp_position
+			wdt = dt_warp(dt);
+			t += dt;
+			// -- hash-grid gather straight into this lane's row of the staging tile ---------------------------------------
+			encode_position_to_row<F, false>(s_levels, model.grid_params, wpos, tile + lane * kTileStrideH, nullptr);
+		}
+		// -- both MLPs ---------------------------------------------------------------------------------------------------
+		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, sh_frag);
 
 		// -- composite -------------------------------------------------------------------------------------------------
 		if (valid) {
@@ -252,7 +275,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			const v3 pos = model.train_aabb.lo + wpos * aabb_diag;   // unwarp_position
 			const float T = 1.f - rgba.w;
 			const float dt = dt_unwarp(wdt);
-			const float alpha = 1.f - expf(-act_density(__high2float(bs), model.density_act) * dt);
+			const float alpha = 1.f - __expf(-act_density(__high2float(bs), model.density_act) * dt);
 			const float weight = alpha * T;
 			v3 rgb = mk3(act_rgb(__low2float(rg), model.rgb_act), act_rgb(__high2float(rg), model.rgb_act), act_rgb(__low2float(bs), model.rgb_act));
 			if (!ALT) {
@@ -268,8 +291,8 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				depth = dot(cam_fwd, pos - view.cam.c3);
 			}
 			if (rgba.w > (1.0f - model.min_transmittance)) {
-				const float a = rgba.w;
-				rgba.x /= a; rgba.y /= a; rgba.z /= a; rgba.w /= a;
+				const float inv_a = 1.0f / rgba.w;
+				rgba.x *= inv_a; rgba.y *= inv_a; rgba.z *= inv_a; rgba.w *= inv_a;
 				finish();
 			} else if (++k == kBatchSteps) {
 				// batch boundary: the sng compositor rewinds t to the last composited sample
@@ -289,9 +312,9 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		n_launched += __shfl_xor_sync(0xFFFFFFFFu, n_launched, s);
 	}
 	if (lane == 0 && counters) {
-		atomicAdd(&counters->samples, n_samples);
-		atomicAdd(&counters->hits, n_hits);
-		atomicAdd(&counters->rays, n_launched);
+		atomicAdd(&counters->samples, (unsigned long long)n_samples);
+		atomicAdd(&counters->hits, (unsigned long long)n_hits);
+		atomicAdd(&counters->rays, (unsigned long long)n_launched);
 	}
 }
 
@@ -329,43 +352,46 @@ __global__ void __launch_bounds__(128) k_march_trace(DevView view, MarchEnv env,
 	n_out[ray] = n;
 }
 
-// NerfNetwork inference on explicit NerfCoordinates (n x 7 floats) through the same warp evaluator as the fused kernel.
+// NerfNetwork inference on explicit NerfCoordinates (n x 7 floats) through the same encode + warp evaluator as the fused kernel.
 template <int F>
 __global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel model, const float* __restrict__ coords, uint64_t n, uint16_t* __restrict__ out,
                                                                      uint16_t* __restrict__ features, uint32_t* __restrict__ hash_idx) {
 	__shared__ __align__(16) uint32_t s_w[kFragWords];
 	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
+	__shared__ LevelDesc s_levels[kMaxLevels];
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
+	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x);
 	__syncthreads();
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
 	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
+	__half* row = tile + lane * kTileStrideH;
 	const uint64_t n_tiles = (n + 31) / 32;
 	for (uint64_t tile_i = (uint64_t)blockIdx.x * kFusedWarps + warp; tile_i < n_tiles; tile_i += (uint64_t)gridDim.x * kFusedWarps) {
 		const uint64_t i = tile_i * 32 + lane;
 		const bool valid = i < n;
-		uint32_t feat[16], sh[8];
-#pragma unroll
-		for (int j = 0; j < 16; ++j) feat[j] = 0u;
+		uint32_t sh[8];
 #pragma unroll
 		for (int j = 0; j < 8; ++j) sh[j] = 0u;
+#pragma unroll
+		for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(row)[j] = make_uint4(0, 0, 0, 0);
 		if (valid) {
 			const float* c = coords + i * 7;
 			const v3 p = mk3(c[0], c[1], c[2]), dir = mk3(c[4], c[5], c[6]);
-			if (hash_idx) encode_position<F>(model.grid, model.grid_params, p, feat, hash_idx + i * (uint64_t)(kFeat / F) * 8);
-			else encode_position<F>(model.grid, model.grid_params, p, feat, nullptr);
+			if (hash_idx) encode_position_to_row<F, true>(s_levels, model.grid_params, p, row, hash_idx + i * (uint64_t)(kFeat / F) * 8);
+			else encode_position_to_row<F, false>(s_levels, model.grid_params, p, row, nullptr);
 			encode_direction_sh4(dir, sh);
 			if (features) {
 #pragma unroll
-				for (int j = 0; j < 16; ++j) reinterpret_cast<uint32_t*>(features)[i * 16 + j] = feat[j];
+				for (int j = 0; j < 16; ++j) reinterpret_cast<uint32_t*>(features)[i * 16 + j] = reinterpret_cast<const uint32_t*>(row)[j];
 			}
 		}
 		stage_sh_row(tile, lane, sh);
 		__syncwarp();
 		uint32_t sh_frag[2][4];
 		load_sh_frags(tile, lane, sh_frag);
-		const uint2 r = warp_network_eval(s_w, tile, out_tile, lane, feat, sh_frag);
+		const uint2 r = warp_network_eval(s_w, tile, out_tile, lane, sh_frag);
 		if (valid) reinterpret_cast<uint2*>(out)[i] = r;
 	}
 }

@@ -54,6 +54,37 @@ SNB_HD uint32_t grid_cell_index(uint32_t hashmap_size, uint32_t res, uint32_t x,
 	return index % hashmap_size;
 }
 
+// Per-level constants of the lookup, 32 B, staged in shared memory once per CTA. `mode` is decided once per level by
+// running the stride rule of grid_cell_index: 0 = dense through all three axes, 1 = hashed, 2 = anything else (generic).
+struct __align__(16) LevelDesc {
+	float scale;
+	uint32_t s1, s2;      // dense strides of y and z (uint32 wrap-around arithmetic, as the reference's)
+	uint32_t size;        // entries of this level
+	uint32_t offset;      // first entry of this level in the concatenated table
+	uint32_t mode;
+	uint32_t mask;        // size - 1 when size is a power of two, else 0
+	uint32_t pad;
+};
+enum { kLevelDense = 0, kLevelHashed = 1, kLevelGeneric = 2 };
+
+SNB_HD LevelDesc make_level_desc(const GridDesc& g, int level) {
+	LevelDesc d;
+	const uint32_t res = g.res[level];
+	d.scale = g.scale[level];
+	d.offset = g.offset[level];
+	d.size = g.offset[level + 1] - g.offset[level];
+	d.s1 = res; d.s2 = res * res;
+	d.mask = (d.size & (d.size - 1u)) == 0u ? d.size - 1u : 0u;
+	d.pad = 0;
+	uint32_t stride = res;
+	bool y_in = false, z_in = false;
+	if (stride <= d.size) { y_in = true; stride *= res; }
+	if (stride <= d.size) { z_in = true; stride *= res; }
+	if (d.size < stride) d.mode = d.mask ? kLevelHashed : kLevelGeneric;
+	else d.mode = (y_in && z_in) ? kLevelDense : kLevelGeneric;
+	return d;
+}
+
 template <int F> struct FeatVec;
 template <> struct FeatVec<1> { typedef unsigned short T; };
 template <> struct FeatVec<2> { typedef uint32_t T; };
@@ -63,37 +94,53 @@ template <> struct FeatVec<8> { typedef uint4 T; };
 SNB_D __half2 u2h2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
 SNB_D uint32_t h22u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 
+__device__ __noinline__ uint32_t slow_mod(uint32_t a, uint32_t b) { return a % b; }
+
 // One level for one sample: 8 corner gathers + fp16 trilinear accumulate. `out` receives F halves packed in F/2
-// words (F == 1: low half of out[0]). idx_out (optional) receives the 8 table indices.
-template <int F>
-SNB_D void encode_level(const GridDesc& g, int level, const __half* __restrict__ table, v3 x, uint32_t* out, uint32_t* idx_out) {
-	const uint32_t lvl_off = g.offset[level];
-	const uint32_t hashmap_size = g.offset[level + 1] - lvl_off;
-	const float scale = g.scale[level];
-	const uint32_t res = g.res[level];
-	float fr[3]; uint32_t pg[3];
-	{
-		float p = fmaf(scale, x.x, 0.5f); float fl = floorf(p); pg[0] = (uint32_t)(int)fl; fr[0] = p - fl;
-		p = fmaf(scale, x.y, 0.5f); fl = floorf(p); pg[1] = (uint32_t)(int)fl; fr[1] = p - fl;
-		p = fmaf(scale, x.z, 0.5f); fl = floorf(p); pg[2] = (uint32_t)(int)fl; fr[2] = p - fl;
+// words (F == 1: low half of out[0]). idx_out (TAP only) receives the 8 table indices.
+// The 8 indices share their per-axis terms (dense: base + {0,1} + {0,s1} + {0,s2}; hashed: (x|x+1) ^ (y*P1 | +P1) ^
+// (z*P2 | +P2)), which is the reference's index for each corner in uint32 arithmetic, evaluated once instead of 8 times.
+template <int F, bool TAP>
+SNB_D void encode_level(const LevelDesc& L, const __half* __restrict__ table, v3 x, uint32_t* out, uint32_t* idx_out) {
+	float px = fmaf(L.scale, x.x, 0.5f), py = fmaf(L.scale, x.y, 0.5f), pz = fmaf(L.scale, x.z, 0.5f);
+	const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
+	const uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
+	const float rx = px - flx, ry = py - fly, rz = pz - flz;
+	const float ax = 1.0f - rx, ay = 1.0f - ry, az = 1.0f - rz;
+	uint32_t idx[8];
+	if (L.mode == kLevelHashed) {
+		const uint32_t hy = gy * 2654435761u, hz = gz * 805459861u;
+		const uint32_t yz0 = hy ^ hz, yz1 = (hy + 2654435761u) ^ hz, yz2 = hy ^ (hz + 805459861u), yz3 = (hy + 2654435761u) ^ (hz + 805459861u);
+		const uint32_t x1 = gx + 1u;
+		idx[0] = (gx ^ yz0) & L.mask; idx[1] = (x1 ^ yz0) & L.mask; idx[2] = (gx ^ yz1) & L.mask; idx[3] = (x1 ^ yz1) & L.mask;
+		idx[4] = (gx ^ yz2) & L.mask; idx[5] = (x1 ^ yz2) & L.mask; idx[6] = (gx ^ yz3) & L.mask; idx[7] = (x1 ^ yz3) & L.mask;
+	} else if (L.mode == kLevelDense) {
+		const uint32_t b0 = gx + gy * L.s1 + gz * L.s2;
+		const uint32_t b1 = b0 + L.s1, b2 = b0 + L.s2, b3 = b1 + L.s2;
+		idx[0] = b0; idx[1] = b0 + 1u; idx[2] = b1; idx[3] = b1 + 1u; idx[4] = b2; idx[5] = b2 + 1u; idx[6] = b3; idx[7] = b3 + 1u;
+#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			if (idx[c] >= L.size) { idx[c] -= L.size; if (idx[c] >= L.size) idx[c] = slow_mod(idx[c], L.size); }
+		}
+	} else {
+		const uint32_t res = L.s1;
+#pragma unroll 1
+		for (int c = 0; c < 8; ++c) idx[c] = grid_cell_index(L.size, res, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
 	}
 	typedef typename FeatVec<F>::T V;
-	const V* base = reinterpret_cast<const V*>(table) + lvl_off;
-	V vals[8]; __half w[8];
+	const V* base = reinterpret_cast<const V*>(table) + L.offset;
+	V vals[8];
 #pragma unroll
-	for (int c = 0; c < 8; ++c) {
-		float weight = 1.0f;
-		uint32_t pl[3];
+	for (int c = 0; c < 8; ++c) vals[c] = __ldg(base + idx[c]);
+	if (TAP) {
 #pragma unroll
-		for (int d = 0; d < 3; ++d) {
-			if ((c & (1 << d)) == 0) { weight *= 1.0f - fr[d]; pl[d] = pg[d]; }
-			else { weight *= fr[d]; pl[d] = pg[d] + 1; }
-		}
-		const uint32_t index = grid_cell_index(hashmap_size, res, pl[0], pl[1], pl[2]);
-		if (idx_out) idx_out[c] = index;
-		vals[c] = __ldg(base + index);
-		w[c] = __float2half_rn(weight);
+		for (int c = 0; c < 8; ++c) idx_out[c] = idx[c];
 	}
+	// weights: ((1 * wx) * wy) * wz, rounded to half once (grid.h:144)
+	const float wxy0 = ax * ay, wxy1 = rx * ay, wxy2 = ax * ry, wxy3 = rx * ry;
+	__half w[8];
+	w[0] = __float2half_rn(wxy0 * az); w[1] = __float2half_rn(wxy1 * az); w[2] = __float2half_rn(wxy2 * az); w[3] = __float2half_rn(wxy3 * az);
+	w[4] = __float2half_rn(wxy0 * rz); w[5] = __float2half_rn(wxy1 * rz); w[6] = __float2half_rn(wxy2 * rz); w[7] = __float2half_rn(wxy3 * rz);
 	if constexpr (F == 1) {
 		__half r = __ushort_as_half((unsigned short)0);
 #pragma unroll
@@ -121,21 +168,20 @@ SNB_D void encode_level(const GridDesc& g, int level, const __half* __restrict__
 	}
 }
 
-// All levels of one sample -> 32 halves in 16 words (level-major, feature-minor, as the reference's AoS row).
-template <int F>
-SNB_D void encode_position(const GridDesc& g, const __half* __restrict__ table, v3 x, uint32_t (&feat)[16], uint32_t* idx_out) {
+// All levels of one sample -> the 32 feature halves of this lane's row of the staging tile (level-major,
+// feature-minor, as the reference's AoS row). The level loop is deliberately not fully unrolled: the fused kernel's
+// hot loop has to stay inside the 32 KB instruction cache (profiles/r01_ncu_fused_v2.md).
+template <int F, bool TAP>
+SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, const __half* __restrict__ table, v3 x, __half* row, uint32_t* idx_out) {
 	constexpr int L = kFeat / F;
-	if constexpr (F == 1) {
-#pragma unroll
-		for (int l = 0; l < L; l += 2) {
-			uint32_t a, b;
-			encode_level<1>(g, l, table, x, &a, idx_out ? idx_out + l * 8 : nullptr);
-			encode_level<1>(g, l + 1, table, x, &b, idx_out ? idx_out + (l + 1) * 8 : nullptr);
-			feat[l / 2] = a | (b << 16);
-		}
-	} else {
-#pragma unroll
-		for (int l = 0; l < L; ++l) encode_level<F>(g, l, table, x, &feat[l * (F / 2)], idx_out ? idx_out + l * 8 : nullptr);
+#pragma unroll 2
+	for (int l = 0; l < L; ++l) {
+		uint32_t o[F >= 2 ? F / 2 : 1];
+		encode_level<F, TAP>(levels[l], table, x, o, TAP ? idx_out + l * 8 : nullptr);
+		if constexpr (F == 1) row[l] = __ushort_as_half((unsigned short)o[0]);
+		else if constexpr (F == 2) reinterpret_cast<uint32_t*>(row)[l] = o[0];
+		else if constexpr (F == 4) reinterpret_cast<uint2*>(row)[l] = make_uint2(o[0], o[1]);
+		else reinterpret_cast<uint4*>(row)[l] = make_uint4(o[0], o[1], o[2], o[3]);
 	}
 }
 
@@ -180,8 +226,9 @@ SNB_D void ldmatrix_x4(uint32_t (&r)[4], const void* smem_row_ptr) {
 	asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
 SNB_D uint32_t pack_relu_h2(float a, float b, bool relu) {
-	if (relu) { a = a < 0.0f ? 0.0f : a; b = b < 0.0f ? 0.0f : b; }
-	return h22u(__floats2half2_rn(a, b));
+	// round first, then clamp both halves with one HMNMX2: max(round(x), 0) == round(max(x, 0)) (rounding is monotonic)
+	const __half2 h = __floats2half2_rn(a, b);
+	return relu ? h22u(__hmax2(h, u2h2(0u))) : h22u(h);
 }
 
 // Load the A fragments (2 m-tiles x KT k-tiles) of a staged [32 x 16*KT] half tile.
@@ -231,19 +278,11 @@ SNB_D void dense_to_frags(const uint32_t* __restrict__ wfrag, int lane, const ui
 }
 
 // Full network for the warp's 32 samples.
-//   feat: this lane's 32 encoded halves; sh_frag: the rays' SH tile already in A-fragment form (constant per ray);
+//   the tile holds each lane's 32 encoded halves in its row; sh_frag: the rays' SH tile already in A-fragment form (constant per ray);
 //   returns this lane's {r, g, b, sigma} as raw fp16 network outputs (activations are applied by the compositor).
 // smem_w: fragment-ordered weights (kFragWords words); tile/out_tile: this warp's staging areas.
-SNB_D uint2 warp_network_eval(const uint32_t* __restrict__ smem_w, __half* tile, __half* out_tile, int lane,
-                             const uint32_t (&feat)[16], const uint32_t (&sh_frag)[2][4]) {
-	// stage features row-major, then pull them back as A fragments
-	{
-		uint4* dst = reinterpret_cast<uint4*>(tile + lane * kTileStrideH);
-		dst[0] = make_uint4(feat[0], feat[1], feat[2], feat[3]);
-		dst[1] = make_uint4(feat[4], feat[5], feat[6], feat[7]);
-		dst[2] = make_uint4(feat[8], feat[9], feat[10], feat[11]);
-		dst[3] = make_uint4(feat[12], feat[13], feat[14], feat[15]);
-	}
+SNB_D uint2 warp_network_eval(const uint32_t* __restrict__ smem_w, __half* tile, __half* out_tile, int lane, const uint32_t (&sh_frag)[2][4]) {
+	// the features were staged row-major by encode_position_to_row; pull them back as A fragments
 	__syncwarp();
 	uint32_t a_feat[2][2][4];
 	load_a_frags<2>(tile, lane, a_feat);
