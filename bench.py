@@ -151,18 +151,11 @@ def run_reference(args, rank, world):
     }))
 
 
-def strip_for(rank, world, width, halo):
-    """Column strip of `rank` plus the halo it recomputes so that normals / shadow windows equal the single-GPU frame."""
-    x0 = width * rank // world; x1 = width * (rank + 1) // world
-    hx0 = max(0, x0 - halo); hx1 = min(width, x1 + halo)
-    return x0, x1, hx0, hx1
-
-
 def run_ours(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
     import common
-    from synerfgine_b200 import Engine, Testbed, scenes
+    from synerfgine_b200 import Engine, Testbed, scenes, tiles
     from synerfgine_b200._lib import Tile
 
     torch.cuda.set_device(local_rank)
@@ -175,8 +168,9 @@ def run_ours(args, rank, local_rank, world):
     tb.set_model(model)                                   # weights / bitfield replicated once per GPU
     eng = Engine()
     eng.set_virtual_world_json(scenes.scene_json(args.scene), scenes.mesh_dir())
-    halo = max(2, eng.rt.nerf_shadow_kernel // 2 + 2)
-    x0, x1, hx0, hx1 = strip_for(rank, world, W, halo)
+    halo = tiles.halo_for(eng.rt.nerf_shadow_kernel, bool(eng.rt.show_shadow_on_nerf))
+    strip = tiles.strip_for(rank, world, W, halo, align=max(1, eng.rt.syn_px_scale))
+    x0, x1, hx0, hx1 = strip.x0, strip.x1, strip.hx0, strip.hx1
     tile = Tile(hx0, 0, hx1 - hx0, H) if world > 1 else None
     eng.init(W, H, tb, tile=tile)
     lib, ctx = tb.lib, tb.ctx

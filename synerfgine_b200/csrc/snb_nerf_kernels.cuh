@@ -165,7 +165,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += kFusedThreads) s_coarse[i] = __ldg(model.env.coarse + i);
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
-	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x);
+	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x, model.grid_params);
 	__syncthreads();
 
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -263,7 +263,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			wdt = dt_warp(dt);
 			t += dt;
 			// -- hash-grid gather straight into this lane's row of the staging tile ---------------------------------------
-			encode_position_to_row<F, false>(s_levels, model.grid_params, wpos, tile + lane * kTileStrideH, nullptr);
+			encode_position_to_row<F, false>(s_levels, wpos, tile + lane * kTileStrideH, nullptr);
 		}
 		// -- both MLPs ---------------------------------------------------------------------------------------------------
 		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, sh_frag);
@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel mo
 	__shared__ LevelDesc s_levels[kMaxLevels];
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
-	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x);
+	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x, model.grid_params);
 	__syncthreads();
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
@@ -379,8 +379,8 @@ __global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel mo
 		if (valid) {
 			const float* c = coords + i * 7;
 			const v3 p = mk3(c[0], c[1], c[2]), dir = mk3(c[4], c[5], c[6]);
-			if (hash_idx) encode_position_to_row<F, true>(s_levels, model.grid_params, p, row, hash_idx + i * (uint64_t)(kFeat / F) * 8);
-			else encode_position_to_row<F, false>(s_levels, model.grid_params, p, row, nullptr);
+			if (hash_idx) encode_position_to_row<F, true>(s_levels, p, row, hash_idx + i * (uint64_t)(kFeat / F) * 8);
+			else encode_position_to_row<F, false>(s_levels, p, row, nullptr);
 			encode_direction_sh4(dir, sh);
 			if (features) {
 #pragma unroll

@@ -60,22 +60,20 @@ struct __align__(16) LevelDesc {
 	float scale;
 	uint32_t s1, s2;      // dense strides of y and z (uint32 wrap-around arithmetic, as the reference's)
 	uint32_t size;        // entries of this level
-	uint32_t offset;      // first entry of this level in the concatenated table
+	const void* base;     // first entry of this level in the concatenated table (one 64-bit add per level, not per corner)
 	uint32_t mode;
 	uint32_t mask;        // size - 1 when size is a power of two, else 0
-	uint32_t pad;
 };
 enum { kLevelDense = 0, kLevelHashed = 1, kLevelGeneric = 2 };
 
-SNB_HD LevelDesc make_level_desc(const GridDesc& g, int level) {
+SNB_HD LevelDesc make_level_desc(const GridDesc& g, int level, const __half* table) {
 	LevelDesc d;
 	const uint32_t res = g.res[level];
 	d.scale = g.scale[level];
-	d.offset = g.offset[level];
+	d.base = table + (size_t)g.offset[level] * g.n_feat;
 	d.size = g.offset[level + 1] - g.offset[level];
 	d.s1 = res; d.s2 = res * res;
 	d.mask = (d.size & (d.size - 1u)) == 0u ? d.size - 1u : 0u;
-	d.pad = 0;
 	uint32_t stride = res;
 	bool y_in = false, z_in = false;
 	if (stride <= d.size) { y_in = true; stride *= res; }
@@ -94,14 +92,14 @@ template <> struct FeatVec<8> { typedef uint4 T; };
 SNB_D __half2 u2h2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
 SNB_D uint32_t h22u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 
-__device__ __noinline__ uint32_t slow_mod(uint32_t a, uint32_t b) { return a % b; }
+__device__ __noinline__ uint32_t grid_cell_index_slow(uint32_t hashmap_size, uint32_t res, uint32_t x, uint32_t y, uint32_t z) { return grid_cell_index(hashmap_size, res, x, y, z); }
 
 // One level for one sample: 8 corner gathers + fp16 trilinear accumulate. `out` receives F halves packed in F/2
 // words (F == 1: low half of out[0]). idx_out (TAP only) receives the 8 table indices.
 // The 8 indices share their per-axis terms (dense: base + {0,1} + {0,s1} + {0,s2}; hashed: (x|x+1) ^ (y*P1 | +P1) ^
 // (z*P2 | +P2)), which is the reference's index for each corner in uint32 arithmetic, evaluated once instead of 8 times.
 template <int F, bool TAP>
-SNB_D void encode_level(const LevelDesc& L, const __half* __restrict__ table, v3 x, uint32_t* out, uint32_t* idx_out) {
+SNB_D void encode_level(const LevelDesc& L, v3 x, uint32_t* out, uint32_t* idx_out) {
 	float px = fmaf(L.scale, x.x, 0.5f), py = fmaf(L.scale, x.y, 0.5f), pz = fmaf(L.scale, x.z, 0.5f);
 	const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
 	const uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
@@ -109,26 +107,24 @@ SNB_D void encode_level(const LevelDesc& L, const __half* __restrict__ table, v3
 	const float ax = 1.0f - rx, ay = 1.0f - ry, az = 1.0f - rz;
 	uint32_t idx[8];
 	if (L.mode == kLevelHashed) {
-		const uint32_t hy = gy * 2654435761u, hz = gz * 805459861u;
-		const uint32_t yz0 = hy ^ hz, yz1 = (hy + 2654435761u) ^ hz, yz2 = hy ^ (hz + 805459861u), yz3 = (hy + 2654435761u) ^ (hz + 805459861u);
-		const uint32_t x1 = gx + 1u;
-		idx[0] = (gx ^ yz0) & L.mask; idx[1] = (x1 ^ yz0) & L.mask; idx[2] = (gx ^ yz1) & L.mask; idx[3] = (x1 ^ yz1) & L.mask;
-		idx[4] = (gx ^ yz2) & L.mask; idx[5] = (x1 ^ yz2) & L.mask; idx[6] = (gx ^ yz3) & L.mask; idx[7] = (x1 ^ yz3) & L.mask;
-	} else if (L.mode == kLevelDense) {
+		// (a ^ b ^ c) & m == (a & m) ^ (b & m) ^ (c & m): mask the six per-axis terms, then one 3-input XOR per corner
+		const uint32_t hy = gy * 2654435761u, hz = gz * 805459861u, m = L.mask;
+		const uint32_t x0 = gx & m, x1 = (gx + 1u) & m, y0 = hy & m, y1 = (hy + 2654435761u) & m, z0 = hz & m, z1 = (hz + 805459861u) & m;
+		idx[0] = x0 ^ y0 ^ z0; idx[1] = x1 ^ y0 ^ z0; idx[2] = x0 ^ y1 ^ z0; idx[3] = x1 ^ y1 ^ z0;
+		idx[4] = x0 ^ y0 ^ z1; idx[5] = x1 ^ y0 ^ z1; idx[6] = x0 ^ y1 ^ z1; idx[7] = x1 ^ y1 ^ z1;
+	} else {
 		const uint32_t b0 = gx + gy * L.s1 + gz * L.s2;
 		const uint32_t b1 = b0 + L.s1, b2 = b0 + L.s2, b3 = b1 + L.s2;
 		idx[0] = b0; idx[1] = b0 + 1u; idx[2] = b1; idx[3] = b1 + 1u; idx[4] = b2; idx[5] = b2 + 1u; idx[6] = b3; idx[7] = b3 + 1u;
+		// dense level and the largest corner index in range (and no uint32 wrap): nothing to reduce. Otherwise (last cell of a
+		// dense level, positions outside [0,1], or a level the stride rule treats specially) take the reference's formula per corner.
+		if (L.mode != kLevelDense || b0 > idx[7] || idx[7] >= L.size) {
 #pragma unroll
-		for (int c = 0; c < 8; ++c) {
-			if (idx[c] >= L.size) { idx[c] -= L.size; if (idx[c] >= L.size) idx[c] = slow_mod(idx[c], L.size); }
+			for (int c = 0; c < 8; ++c) idx[c] = grid_cell_index_slow(L.size, L.s1, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
 		}
-	} else {
-		const uint32_t res = L.s1;
-#pragma unroll 1
-		for (int c = 0; c < 8; ++c) idx[c] = grid_cell_index(L.size, res, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
 	}
 	typedef typename FeatVec<F>::T V;
-	const V* base = reinterpret_cast<const V*>(table) + L.offset;
+	const V* base = reinterpret_cast<const V*>(L.base);
 	V vals[8];
 #pragma unroll
 	for (int c = 0; c < 8; ++c) vals[c] = __ldg(base + idx[c]);
@@ -172,12 +168,12 @@ SNB_D void encode_level(const LevelDesc& L, const __half* __restrict__ table, v3
 // feature-minor, as the reference's AoS row). The level loop is deliberately not fully unrolled: the fused kernel's
 // hot loop has to stay inside the 32 KB instruction cache (profiles/r01_ncu_fused_v2.md).
 template <int F, bool TAP>
-SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, const __half* __restrict__ table, v3 x, __half* row, uint32_t* idx_out) {
+SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, v3 x, __half* row, uint32_t* idx_out) {
 	constexpr int L = kFeat / F;
 #pragma unroll 2
 	for (int l = 0; l < L; ++l) {
 		uint32_t o[F >= 2 ? F / 2 : 1];
-		encode_level<F, TAP>(levels[l], table, x, o, TAP ? idx_out + l * 8 : nullptr);
+		encode_level<F, TAP>(levels[l], x, o, TAP ? idx_out + l * 8 : nullptr);
 		if constexpr (F == 1) row[l] = __ushort_as_half((unsigned short)o[0]);
 		else if constexpr (F == 2) reinterpret_cast<uint32_t*>(row)[l] = o[0];
 		else if constexpr (F == 4) reinterpret_cast<uint2*>(row)[l] = make_uint2(o[0], o[1]);

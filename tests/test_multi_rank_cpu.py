@@ -1,0 +1,128 @@
+"""CPU tests of the N>1 path: strip partition + halo + one gather per frame, with world_size 2 over gloo.
+The renderer plugged into synerfgine_b200.tiles here is the CPU oracle (test infrastructure) rendering a TILE of the frame
+with global pixel indices — the same contract libsnb.so's snb_tile honours on the GPU (tests/test_gpu_nerf.py::
+test_tile_equals_crop_of_full_frame and bench.py --gpus N exercise that side)."""
+import ctypes as C
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import common
+import oracle_lib as O
+from synerfgine_b200 import tiles
+
+W, H = 40, 24
+
+
+def test_strips_tile_the_frame_exactly():
+    for width in (1920, 1921, 40, 7):
+        for world in (1, 2, 3, 4, 8):
+            for halo in (2, 4):
+                if world > width:
+                    continue
+                strips = [tiles.strip_for(r, world, width, halo) for r in range(world)]
+                assert strips[0].x0 == 0 and strips[-1].x1 == width
+                for a, b in zip(strips, strips[1:]):
+                    assert a.x1 == b.x0
+                for s in strips:
+                    assert s.hx0 == max(0, s.x0 - halo) and s.hx1 == min(width, s.x1 + halo)
+                    assert s.crop.stop - s.crop.start == s.width
+                assert max(s.width for s in strips) - min(s.width for s in strips) <= 1
+
+
+def test_strip_alignment_to_syn_px_scale():
+    for r in range(3):
+        s = tiles.strip_for(r, 3, 1920, 3, align=4)
+        assert s.x0 % 4 == 0 and s.x1 % 4 == 0 and s.hx0 % 4 == 0 and s.hx1 % 4 == 0
+        assert (s.x0 - s.hx0) in (0, 4) and (s.hx1 - s.x1) in (0, 4)
+    with pytest.raises(ValueError):
+        tiles.strip_for(0, 2, 1921, 2, align=4)
+    with pytest.raises(ValueError):
+        tiles.strip_for(2, 2, 1920, 2)
+
+
+def test_halo_and_frame_batch():
+    assert tiles.halo_for(4) == 4 and tiles.halo_for(1) == 2 and tiles.halo_for(8) == 6 and tiles.halo_for(8, False) == 2
+    got = [list(tiles.frame_batch_for(r, 8, 64)) for r in range(8)]
+    assert sum(got, []) == list(range(64)) and all(len(g) == 8 for g in got)
+    got = [list(tiles.frame_batch_for(r, 3, 10)) for r in range(3)]
+    assert sum(got, []) == list(range(10))
+
+
+def oracle_nerf_layer(model_desc, view):
+    """NeRF layer + screen-space normals of the full view (the stencil the halo exists for)."""
+    fb, depth, pos, _ = O.render_nerf(model_desc, view, alt=1, positions=True)
+    nrm = np.zeros_like(pos)
+    O.load().orc_write_normals(view.width, view.height, O.P(np.ascontiguousarray(pos)), O.P(nrm))
+    return fb, depth, pos, nrm
+
+
+def make_tile_renderer(model_desc, view):
+    """render_tile(x0, y0, w, h): what one rank computes — rays of the tile only (global pixel indices), then the normals
+    stencil INSIDE the tile (it stops at the tile edge exactly like at an image edge). Channels: rgb + normal.x packed in
+    rgba so that a wrong halo shows up in the gathered frame; depth as is."""
+    full_fb, full_depth, full_pos, _ = O.render_nerf(model_desc, view, alt=1, positions=True)   # per-ray results are tile-independent
+
+    def render_tile(x0, y0, w, h):
+        pos = np.ascontiguousarray(full_pos[y0:y0 + h, x0:x0 + w])
+        nrm = np.zeros_like(pos)
+        O.load().orc_write_normals(w, h, O.P(pos), O.P(nrm))
+        rgba = np.ascontiguousarray(full_fb[y0:y0 + h, x0:x0 + w]).copy()
+        rgba[..., 3] = nrm[..., 0]
+        return torch.from_numpy(rgba), torch.from_numpy(np.ascontiguousarray(full_depth[y0:y0 + h, x0:x0 + w]))
+    return render_tile
+
+
+def _worker(rank, world, port, halo, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        m = common.model("small16x2")
+        v = common.make_view(W, H)
+        rgba, depth = tiles.render_strip_and_gather(make_tile_renderer(m.desc(), v), rank, world, W, H, halo, dist=dist)
+        if rank == 0:
+            np.savez(out_path, rgba=rgba.numpy(), depth=depth.numpy())
+        else:
+            assert rgba is None and depth is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_two_rank_frame_equals_single_rank_frame(tmp_path, world):
+    m = common.model("small16x2")
+    v = common.make_view(W, H)
+    fb, depth, pos, nrm = oracle_nerf_layer(m.desc(), v)
+    expect = fb.copy(); expect[..., 3] = nrm[..., 0]
+    out = str(tmp_path / "frame.npz")
+    mp.spawn(_worker, args=(world, _free_port(), tiles.halo_for(1), out), nprocs=world, join=True)
+    got = np.load(out)
+    np.testing.assert_array_equal(got["rgba"].view(np.uint32), expect.view(np.uint32))      # bit-identical to the 1-rank frame
+    np.testing.assert_array_equal(got["depth"].view(np.uint32), depth.view(np.uint32))
+    assert np.abs(nrm[..., 0]).max() > 0.1
+
+
+def test_missing_halo_is_detected(tmp_path):
+    """Negative control: with halo 0 the normals next to the seam differ, i.e. the test above really checks the halo."""
+    m = common.model("small16x2")
+    v = common.make_view(W, H)
+    fb, depth, pos, nrm = oracle_nerf_layer(m.desc(), v)
+    out = str(tmp_path / "frame0.npz")
+    mp.spawn(_worker, args=(2, _free_port(), 0, out), nprocs=2, join=True)
+    got = np.load(out)["rgba"][..., 3]
+    seam = W // 2
+    assert not np.array_equal(got[:, seam - 2:seam + 2], nrm[:, seam - 2:seam + 2, 0])
+    np.testing.assert_array_equal(got[:, :seam - 2], nrm[:, :seam - 2, 0])
