@@ -208,6 +208,7 @@ def run_ours(args, rank, local_rank, world):
             for k_, v_ in st.items():
                 stage_acc[k_] = stage_acc.get(k_, 0.0) + v_ / K
             c = tb.counters(); samples += c["samples"]; rays += c["rays"]
+            march_stats = tb.march_stats()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -260,7 +261,7 @@ def run_ours(args, rank, local_rank, world):
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32 march / f16 MLP (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "resolution": [W, H], "scene": args.scene, "parallelism": f"{world} column strips, halo {halo}px" if world > 1 else "single GPU",
-                       "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples / K, "rays_marched_per_frame": rays / K,
+                       "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples / K, "rays_marched_per_frame": rays / K, "march_stats_last_frame": march_stats,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()}},
             "e2e": {"value": n_rays_total * K / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / K * 1e3},
             "gpu_launches": launches,

@@ -164,6 +164,9 @@ int snb_network_inference(snb_ctx* ctx, const float* coords_dev, uint64_t n, uin
 int snb_trace_rays(snb_ctx* ctx, const float* rays_dev, uint32_t n, int32_t* obj_id_dev, int32_t* tri_id_dev, float* t_dev);
 /* Counters of the last NeRF render: [0] network samples, [1] rays launched, [2] rays that hit, [3] march batches. */
 int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
+/* Scheduling statistics of the last NeRF march (instrumentation; SURVEY.md 8d "device counters"): [0] pool iterations summed
+ * over CTAs, [1] empty-space DDA steps, [2] search passes (warp level), [3] CTAs of the persistent grid. */
+int snb_get_march_stats(snb_ctx* ctx, uint64_t* out4_host);
 /* Device time (ms, CUDA events on the context's stream) of the stages of the last frame: [0] NeRF ray generation,
  * [1] fused NeRF march kernel, [2] normals + mesh shadows on the NeRF, [3] mesh layer, [4] overlay. Synchronises. */
 int snb_get_stage_ms(snb_ctx* ctx, float* out5_host);

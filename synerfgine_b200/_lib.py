@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsnb.so")
+LIB_PATH = os.environ.get("SNB_LIB") or os.path.join(_HERE, "libsnb.so")   # SNB_LIB: alternative build of the same library (tuning runs)
 
 f32, u32, i32, u64, u16, u8 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64, C.c_uint16, C.c_uint8
 pf32 = C.POINTER(f32)
@@ -79,6 +79,7 @@ SIGNATURES = {
     "snb_network_inference": (C.c_int, [vp, vp, u64, vp, vp, vp]),
     "snb_trace_rays": (C.c_int, [vp, vp, u32, vp, vp, vp]),
     "snb_get_counters": (C.c_int, [vp, C.POINTER(u64)]),
+    "snb_get_march_stats": (C.c_int, [vp, C.POINTER(u64)]),
     "snb_get_stage_ms": (C.c_int, [vp, pf32]),
     "snb_launch_count": (u64, [vp]),
     "snb_scene_load_json": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),

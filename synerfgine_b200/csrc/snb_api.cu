@@ -5,6 +5,7 @@
 // every host<->device sync inside the frame: the march loop is device-resident, so a frame is a fixed sequence of
 // launches on one stream.
 #include <cstring>
+#include <cstdlib>
 #include <cmath>
 #include <algorithm>
 #include "snb_context.cuh"
@@ -51,6 +52,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	snb_ctx* c = new snb_ctx();
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
+	if (const char* mv = getenv("SNB_MARCH")) c->march_variant = (mv[0] == 'v' && mv[1] == '3') ? 3 : 4;
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
 	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }

@@ -23,7 +23,7 @@ constexpr int kBatchSteps = 8;       // n_steps_between_compaction for <= 262144
 constexpr int kFusedWarps = 4;
 constexpr int kFusedThreads = kFusedWarps * 32;
 
-struct NerfCounters { unsigned long long samples, rays, hits, batches; };
+struct NerfCounters { unsigned long long samples, rays, hits, batches, iterations, dda_steps, net_phases, reserved; };
 
 struct NerfOut {                     // tile-sized output buffers
 	float4* fb;                      // rgba

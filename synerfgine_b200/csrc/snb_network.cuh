@@ -94,17 +94,18 @@ SNB_D uint32_t h22u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 
 __device__ __noinline__ uint32_t grid_cell_index_slow(uint32_t hashmap_size, uint32_t res, uint32_t x, uint32_t y, uint32_t z) { return grid_cell_index(hashmap_size, res, x, y, z); }
 
-// One level for one sample: 8 corner gathers + fp16 trilinear accumulate. `out` receives F halves packed in F/2
-// words (F == 1: low half of out[0]). idx_out (TAP only) receives the 8 table indices.
+// ---- one level, split in two halves so that the gathers of several levels can be in flight together ---------------
 // The 8 indices share their per-axis terms (dense: base + {0,1} + {0,s1} + {0,s2}; hashed: (x|x+1) ^ (y*P1 | +P1) ^
 // (z*P2 | +P2)), which is the reference's index for each corner in uint32 arithmetic, evaluated once instead of 8 times.
+struct LevelFrac { float rx, ry, rz; };
+
+// Part 1: position in the level, corner indices (idx_out for the parity tap), issue the 8 gathers.
 template <int F, bool TAP>
-SNB_D void encode_level(const LevelDesc& L, v3 x, uint32_t* out, uint32_t* idx_out) {
-	float px = fmaf(L.scale, x.x, 0.5f), py = fmaf(L.scale, x.y, 0.5f), pz = fmaf(L.scale, x.z, 0.5f);
+SNB_D void level_gather(const LevelDesc& L, v3 x, typename FeatVec<F>::T (&vals)[8], LevelFrac& fr, uint32_t* idx_out) {
+	const float px = fmaf(L.scale, x.x, 0.5f), py = fmaf(L.scale, x.y, 0.5f), pz = fmaf(L.scale, x.z, 0.5f);
 	const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
 	const uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
-	const float rx = px - flx, ry = py - fly, rz = pz - flz;
-	const float ax = 1.0f - rx, ay = 1.0f - ry, az = 1.0f - rz;
+	fr.rx = px - flx; fr.ry = py - fly; fr.rz = pz - flz;
 	uint32_t idx[8];
 	if (L.mode == kLevelHashed) {
 		// (a ^ b ^ c) & m == (a & m) ^ (b & m) ^ (c & m): mask the six per-axis terms, then one 3-input XOR per corner
@@ -125,14 +126,20 @@ SNB_D void encode_level(const LevelDesc& L, v3 x, uint32_t* out, uint32_t* idx_o
 	}
 	typedef typename FeatVec<F>::T V;
 	const V* base = reinterpret_cast<const V*>(L.base);
-	V vals[8];
 #pragma unroll
 	for (int c = 0; c < 8; ++c) vals[c] = __ldg(base + idx[c]);
 	if (TAP) {
 #pragma unroll
 		for (int c = 0; c < 8; ++c) idx_out[c] = idx[c];
 	}
-	// weights: ((1 * wx) * wy) * wz, rounded to half once (grid.h:144)
+}
+
+// Part 2: trilinear weights ((1 * wx) * wy) * wz rounded to half once (grid.h:144), fp16 FMA accumulate in corner order.
+// `out` receives F halves packed in F/2 words (F == 1: low half of out[0]).
+template <int F>
+SNB_D void level_blend(const typename FeatVec<F>::T (&vals)[8], const LevelFrac& fr, uint32_t* out) {
+	const float rx = fr.rx, ry = fr.ry, rz = fr.rz;
+	const float ax = 1.0f - rx, ay = 1.0f - ry, az = 1.0f - rz;
 	const float wxy0 = ax * ay, wxy1 = rx * ay, wxy2 = ax * ry, wxy3 = rx * ry;
 	__half w[8];
 	w[0] = __float2half_rn(wxy0 * az); w[1] = __float2half_rn(wxy1 * az); w[2] = __float2half_rn(wxy2 * az); w[3] = __float2half_rn(wxy3 * az);
@@ -165,19 +172,31 @@ SNB_D void encode_level(const LevelDesc& L, v3 x, uint32_t* out, uint32_t* idx_o
 }
 
 // All levels of one sample -> the 32 feature halves of this lane's row of the staging tile (level-major,
-// feature-minor, as the reference's AoS row). The level loop is deliberately not fully unrolled: the fused kernel's
-// hot loop has to stay inside the 32 KB instruction cache (profiles/r01_ncu_fused_v2.md).
+// feature-minor, as the reference's AoS row). Levels are processed in groups of G: all 8*G gathers of a group are issued
+// before the first one is consumed, so a sample pays L/G dependent L2 round trips instead of L (with in-order issue a plain
+// unrolled loop serialises them: each level's HFMA chain blocks the next level's loads). The group loop itself is not
+// unrolled: the march kernel's hot loop has to stay inside the instruction cache (profiles/r01_ncu_fused_v2.md).
 template <int F, bool TAP>
 SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, v3 x, __half* row, uint32_t* idx_out) {
 	constexpr int L = kFeat / F;
-#pragma unroll 2
-	for (int l = 0; l < L; ++l) {
-		uint32_t o[F >= 2 ? F / 2 : 1];
-		encode_level<F, TAP>(levels[l], x, o, TAP ? idx_out + l * 8 : nullptr);
-		if constexpr (F == 1) row[l] = __ushort_as_half((unsigned short)o[0]);
-		else if constexpr (F == 2) reinterpret_cast<uint32_t*>(row)[l] = o[0];
-		else if constexpr (F == 4) reinterpret_cast<uint2*>(row)[l] = make_uint2(o[0], o[1]);
-		else reinterpret_cast<uint4*>(row)[l] = make_uint4(o[0], o[1], o[2], o[3]);
+	constexpr int G = F <= 2 ? 2 : 1;
+	typedef typename FeatVec<F>::T V;
+#pragma unroll 1
+	for (int l0 = 0; l0 < L; l0 += G) {
+		V vals[G][8];
+		LevelFrac fr[G];
+#pragma unroll
+		for (int g = 0; g < G; ++g) level_gather<F, TAP>(levels[l0 + g], x, vals[g], fr[g], TAP ? idx_out + (l0 + g) * 8 : nullptr);
+#pragma unroll
+		for (int g = 0; g < G; ++g) {
+			uint32_t o[F >= 2 ? F / 2 : 1];
+			level_blend<F>(vals[g], fr[g], o);
+			const int l = l0 + g;
+			if constexpr (F == 1) row[l] = __ushort_as_half((unsigned short)o[0]);
+			else if constexpr (F == 2) reinterpret_cast<uint32_t*>(row)[l] = o[0];
+			else if constexpr (F == 4) reinterpret_cast<uint2*>(row)[l] = make_uint2(o[0], o[1]);
+			else reinterpret_cast<uint4*>(row)[l] = make_uint4(o[0], o[1], o[2], o[3]);
+		}
 	}
 }
 
@@ -242,7 +261,12 @@ SNB_D void load_a_frags(const __half* tile, int lane, uint32_t (&a)[2][KT][4]) {
 
 // One dense layer for the warp's 32 rows. Output n-tiles [NT0, NT0 + 2*KT_OUT) are produced two at a time and
 // folded straight into the next layer's A fragments (C fragment of n-tiles 2k,2k+1 == A fragment of k-tile k).
-template <int KT_IN, int KT_OUT, bool RELU>
+template <bool GLOBAL_W> SNB_D uint2 load_wfrag(const uint32_t* p) {
+	if (GLOBAL_W) return __ldg(reinterpret_cast<const uint2*>(p));   // weights read through L1 (read-only path)
+	return *reinterpret_cast<const uint2*>(p);                       // weights staged in shared memory
+}
+
+template <int KT_IN, int KT_OUT, bool RELU, bool GLOBAL_W>
 SNB_D void dense_to_frags(const uint32_t* __restrict__ wfrag, int lane, const uint32_t (&a)[2][KT_IN][4], uint32_t (&out)[2][KT_OUT][4]) {
 #pragma unroll
 	for (int ko = 0; ko < KT_OUT; ++ko) {
@@ -258,7 +282,7 @@ SNB_D void dense_to_frags(const uint32_t* __restrict__ wfrag, int lane, const ui
 			const int nt = 2 * ko + h;
 #pragma unroll
 			for (int kt = 0; kt < KT_IN; ++kt) {
-				const uint2 b = *reinterpret_cast<const uint2*>(wfrag + ((nt * KT_IN + kt) * 32 + lane) * 2);
+				const uint2 b = load_wfrag<GLOBAL_W>(wfrag + ((nt * KT_IN + kt) * 32 + lane) * 2);
 				mma16816(acc[0][h], a[0][kt], b.x, b.y);
 				mma16816(acc[1][h], a[1][kt], b.x, b.y);
 			}
@@ -277,26 +301,27 @@ SNB_D void dense_to_frags(const uint32_t* __restrict__ wfrag, int lane, const ui
 //   the tile holds each lane's 32 encoded halves in its row; sh_frag: the rays' SH tile already in A-fragment form (constant per ray);
 //   returns this lane's {r, g, b, sigma} as raw fp16 network outputs (activations are applied by the compositor).
 // smem_w: fragment-ordered weights (kFragWords words); tile/out_tile: this warp's staging areas.
+template <bool GLOBAL_W = false>
 SNB_D uint2 warp_network_eval(const uint32_t* __restrict__ smem_w, __half* tile, __half* out_tile, int lane, const uint32_t (&sh_frag)[2][4]) {
 	// the features were staged row-major by encode_position_to_row; pull them back as A fragments
 	__syncwarp();
 	uint32_t a_feat[2][2][4];
 	load_a_frags<2>(tile, lane, a_feat);
 	uint32_t h1[2][4][4];
-	dense_to_frags<2, 4, true>(smem_w + kFragDW1, lane, a_feat, h1);          // 32 -> 64, ReLU
+	dense_to_frags<2, 4, true, GLOBAL_W>(smem_w + kFragDW1, lane, a_feat, h1);          // 32 -> 64, ReLU
 	uint32_t rgb_in[2][2][4];
 	{
 		uint32_t dens[2][1][4];
-		dense_to_frags<4, 1, false>(smem_w + kFragDW2, lane, h1, dens);        // 64 -> 16
+		dense_to_frags<4, 1, false, GLOBAL_W>(smem_w + kFragDW2, lane, h1, dens);        // 64 -> 16
 #pragma unroll
 		for (int m = 0; m < 2; ++m)
 #pragma unroll
 			for (int i = 0; i < 4; ++i) { rgb_in[m][0][i] = dens[m][0][i]; rgb_in[m][1][i] = sh_frag[m][i]; }
 	}
 	uint32_t g1[2][4][4];
-	dense_to_frags<2, 4, true>(smem_w + kFragRW1, lane, rgb_in, g1);          // 32 -> 64, ReLU
+	dense_to_frags<2, 4, true, GLOBAL_W>(smem_w + kFragRW1, lane, rgb_in, g1);          // 32 -> 64, ReLU
 	uint32_t g2[2][4][4];
-	dense_to_frags<4, 4, true>(smem_w + kFragRW2, lane, g1, g2);              // 64 -> 64, ReLU
+	dense_to_frags<4, 4, true, GLOBAL_W>(smem_w + kFragRW2, lane, g1, g2);              // 64 -> 64, ReLU
 	// last layer: only n-tile 0 (outputs 0..7; rgb = 0..2) is needed
 	float acc[2][4];
 #pragma unroll
@@ -305,7 +330,7 @@ SNB_D uint2 warp_network_eval(const uint32_t* __restrict__ smem_w, __half* tile,
 		for (int i = 0; i < 4; ++i) acc[m][i] = 0.0f;
 #pragma unroll
 	for (int kt = 0; kt < 4; ++kt) {
-		const uint2 b = *reinterpret_cast<const uint2*>(smem_w + kFragRW3 + (kt * 32 + lane) * 2);
+		const uint2 b = load_wfrag<GLOBAL_W>(smem_w + kFragRW3 + (kt * 32 + lane) * 2);
 		mma16816(acc[0], g2[0][kt], b.x, b.y);
 		mma16816(acc[1], g2[1][kt], b.x, b.y);
 	}

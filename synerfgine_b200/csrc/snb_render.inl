@@ -21,17 +21,28 @@ static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
 
 template <int F, bool ALT>
 static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px) {
-	static int per_sm = 0;   // per template instance
+	unsigned int* qctl = c->d_qctl.as<unsigned int>();
+	if (c->march_variant == 3) {   // previous form (one ray per lane), kept for A/B measurements: SNB_MARCH=v3
+		static int per_sm = 0;   // per template instance
+		if (per_sm == 0) {
+			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, 0));
+			per_sm = std::max(1, per_sm);
+		}
+		c->fused_blocks_per_sm = per_sm;
+		const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + kFusedThreads - 1) / kFusedThreads));
+		k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, dv, out, render_mode, c->d_queue.as<RayRec>(), qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+		SNB_LAUNCHED(c);
+		return SNB_OK;
+	}
+	static int per_sm = 0;
 	if (per_sm == 0) {
-		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, 0));
+		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_pool<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PoolSmem)));
+		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_pool<F, ALT>, kPoolThreads, sizeof(PoolSmem)));
 		per_sm = std::max(1, per_sm);
 	}
 	c->fused_blocks_per_sm = per_sm;
-	const int max_blocks = c->sm_count * per_sm;
-	const int want = (n_px + kFusedThreads - 1) / kFusedThreads;
-	const int blocks = std::max(1, std::min(max_blocks, want));
-	unsigned int* qctl = c->d_qctl.as<unsigned int>();
-	k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, dv, out, render_mode, c->d_queue.as<RayRec>(), qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+	const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + kPoolSlots - 1) / kPoolSlots));
+	k_nerf_march_pool<F, ALT><<<blocks, kPoolThreads, sizeof(PoolSmem), c->stream>>>(c->model, dv, out, render_mode, c->d_queue.as<RayRec>(), qctl, qctl + 1, c->d_counters.as<NerfCounters>());
 	SNB_LAUNCHED(c);
 	return SNB_OK;
 }

@@ -85,6 +85,16 @@ int snb_get_counters(snb_ctx* c, uint64_t* out4) {
 	return SNB_OK;
 }
 
+int snb_get_march_stats(snb_ctx* c, uint64_t* out4) {
+	if (!c || !out4) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	NerfCounters h;
+	SNB_CUDA(c, cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	out4[0] = h.iterations; out4[1] = h.dda_steps; out4[2] = h.net_phases; out4[3] = (uint64_t)c->fused_blocks_per_sm * (uint64_t)c->sm_count;
+	return SNB_OK;
+}
+
 int snb_get_stage_ms(snb_ctx* c, float* out5) {
 	if (!c || !out5) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));

@@ -132,6 +132,11 @@ class Testbed:
         self._check(self.lib.snb_get_counters(self.ctx, out), "snb_get_counters")
         return {"samples": out[0], "rays": out[1], "hits": out[2]}
 
+    def march_stats(self):
+        out = (C.c_uint64 * 4)()
+        self._check(self.lib.snb_get_march_stats(self.ctx, out), "snb_get_march_stats")
+        return {"pool_iterations": out[0], "dda_steps": out[1], "search_passes": out[2], "ctas": out[3]}
+
     def stage_ms(self):
         """Device time of the last frame's stages (synchronises): nerf_raygen, nerf_march, nerf_post, mesh, overlay."""
         out = (C.c_float * 5)()
