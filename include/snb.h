@@ -116,6 +116,9 @@ void snb_destroy(snb_ctx* ctx);
 const char* snb_last_error(const snb_ctx* ctx);
 int snb_sync(snb_ctx* ctx);
 const char* snb_version(void);
+/* Implementation selectors (A/B measurements; results are identical within the parity contract): "march" = "pool" | "lane",
+ * "mlp" = "mma" (warp-level mma.sync) | "tc" (CTA-level tcgen05 + TMEM). Environment SNB_MARCH / SNB_MLP set the defaults. */
+int snb_set_option(snb_ctx* ctx, const char* key, const char* value);
 
 /* ---- inputs ------------------------------------------------------------------------------------------- */
 /* ≙ Testbed::load_snapshot result handed over as arrays (src/testbed.cu:4878-4992). */

@@ -63,6 +63,7 @@ SIGNATURES = {
     "snb_last_error": (C.c_char_p, [vp]),
     "snb_sync": (C.c_int, [vp]),
     "snb_version": (C.c_char_p, []),
+    "snb_set_option": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
     "snb_set_model": (C.c_int, [vp, C.POINTER(ModelDesc)]),
     "snb_set_scene": (C.c_int, [vp, C.POINTER(Object), u32, C.POINTER(Material), u32, C.POINTER(Light), u32]),
     "snb_update_scene": (C.c_int, [vp, C.POINTER(Object), u32, C.POINTER(Material), u32, C.POINTER(Light), u32]),

@@ -37,6 +37,21 @@ static GridDesc make_grid_desc(uint32_t n_levels, uint32_t F, uint32_t log2_T, u
 
 extern "C" {
 
+int snb_set_option(snb_ctx* c, const char* key, const char* value) {
+	if (!c || !key || !value) return SNB_ERR_ARG;
+	const std::string k(key), v(value);
+	if (k == "march") {
+		if (v == "v3" || v == "lane") c->march_variant = 3;
+		else if (v == "v4" || v == "pool") c->march_variant = 4;
+		else return c->fail(SNB_ERR_ARG, "march: expected lane | pool");
+	} else if (k == "mlp") {
+		if (v == "mma") c->mlp_variant = 0;
+		else if (v == "tc") c->mlp_variant = 1;
+		else return c->fail(SNB_ERR_ARG, "mlp: expected mma | tc");
+	} else return c->fail(SNB_ERR_ARG, "unknown option");
+	return SNB_OK;
+}
+
 const char* snb_version(void) { return "synerfgine_b200 0.1 (sm_100a)"; }
 
 int snb_create(int device, void* cuda_stream, snb_ctx** out) {
@@ -52,7 +67,8 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	snb_ctx* c = new snb_ctx();
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
-	if (const char* mv = getenv("SNB_MARCH")) c->march_variant = (mv[0] == 'v' && mv[1] == '3') ? 3 : 4;
+	if (const char* mv = getenv("SNB_MARCH")) snb_set_option(c, "march", mv);
+	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
 	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
@@ -102,6 +118,10 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	std::vector<uint32_t> frag(kFragWords);
 	build_mma_fragments(m->params, frag.data());
 	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp_frag.p, frag.data(), kFragWords * 4, cudaMemcpyHostToDevice, c->stream));
+	std::vector<uint16_t> umma(kMlpHalves);
+	tc::build_umma_weights(m->params, umma.data());
+	SNB_CUDA(c, c->d_mlp_umma.reserve(kMlpHalves * 2));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp_umma.p, umma.data(), kMlpHalves * 2, cudaMemcpyHostToDevice, c->stream));
 	const size_t bf_bytes = (size_t)kCascades * kGridCells / 8;
 	if (m->bitfield) {
 		SNB_CUDA(c, c->d_bitfield.reserve(bf_bytes));
@@ -114,7 +134,7 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	d.grid_params = c->d_grid.as<__half>();
 	d.mlp_rowmajor = c->d_mlp.as<__half>();
 	d.mlp_frag = c->d_mlp_frag.as<uint32_t>();
-	d.mlp_umma = nullptr;
+	d.mlp_umma = c->d_mlp_umma.as<__half>();
 	d.train_aabb.lo = ld3(m->aabb_min); d.train_aabb.hi = ld3(m->aabb_max);
 	d.rgb_act = m->rgb_activation; d.density_act = m->density_activation;
 	d.min_transmittance = m->min_transmittance;

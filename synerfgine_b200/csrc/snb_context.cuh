@@ -12,6 +12,7 @@
 #include "snb_device.cuh"
 #include "snb_nerf_kernels.cuh"
 #include "snb_pool_kernel.cuh"
+#include "snb_mlp_tc.cuh"
 #include "snb_sng_kernels.cuh"
 
 namespace snb {
@@ -65,6 +66,7 @@ struct snb_ctx {
 	int syn_w = 0, syn_h = 0;
 	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
+	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
 	int march_variant = 4;             // 4 = ray-pool kernel (snb_pool_kernel.cuh); 3 = one ray per lane (SNB_MARCH=v3, A/B only)
 
 	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)

@@ -176,7 +176,9 @@ SNB_D void level_blend(const typename FeatVec<F>::T (&vals)[8], const LevelFrac&
 // before the first one is consumed, so a sample pays L/G dependent L2 round trips instead of L (with in-order issue a plain
 // unrolled loop serialises them: each level's HFMA chain blocks the next level's loads). The group loop itself is not
 // unrolled: the march kernel's hot loop has to stay inside the instruction cache (profiles/r01_ncu_fused_v2.md).
-template <int F, bool TAP>
+// CS = byte stride between consecutive 16-byte chunks (8 halves) of the row: 16 for a plain row-major tile, 128 for the
+// tcgen05 K-major core-matrix layout (snb_mlp_tc.cuh).
+template <int F, bool TAP, int CS = 16>
 SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, v3 x, __half* row, uint32_t* idx_out) {
 	constexpr int L = kFeat / F;
 	constexpr int G = F <= 2 ? 2 : 1;
@@ -192,10 +194,11 @@ SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, v3 x, __
 			uint32_t o[F >= 2 ? F / 2 : 1];
 			level_blend<F>(vals[g], fr[g], o);
 			const int l = l0 + g;
-			if constexpr (F == 1) row[l] = __ushort_as_half((unsigned short)o[0]);
-			else if constexpr (F == 2) reinterpret_cast<uint32_t*>(row)[l] = o[0];
-			else if constexpr (F == 4) reinterpret_cast<uint2*>(row)[l] = make_uint2(o[0], o[1]);
-			else reinterpret_cast<uint4*>(row)[l] = make_uint4(o[0], o[1], o[2], o[3]);
+			unsigned char* rb = reinterpret_cast<unsigned char*>(row);
+			if constexpr (F == 1) *reinterpret_cast<__half*>(rb + (l / 8) * CS + (l % 8) * 2) = __ushort_as_half((unsigned short)o[0]);
+			else if constexpr (F == 2) *reinterpret_cast<uint32_t*>(rb + (l / 4) * CS + (l % 4) * 4) = o[0];
+			else if constexpr (F == 4) *reinterpret_cast<uint2*>(rb + (l / 2) * CS + (l % 2) * 8) = make_uint2(o[0], o[1]);
+			else *reinterpret_cast<uint4*>(rb + l * CS) = make_uint4(o[0], o[1], o[2], o[3]);
 		}
 	}
 }

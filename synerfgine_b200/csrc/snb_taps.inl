@@ -54,6 +54,23 @@ int snb_network_inference(snb_ctx* c, const float* coords_dev, uint64_t n, uint1
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model");
 	if (n == 0) return SNB_OK;
 	SNB_CUDA(c, cudaSetDevice(c->device));
+	if (c->mlp_variant == 1) {
+		const uint64_t tiles = (n + tc::kTileRows - 1) / tc::kTileRows;
+		const int blocks = (int)std::min<uint64_t>(tiles, (uint64_t)c->sm_count * 2);
+		const int smem = tc::kSmemBytes + 1024 + (int)sizeof(LevelDesc) * kMaxLevels;
+#define SNB_TC_TAP(FF) do { \
+		SNB_CUDA(c, cudaFuncSetAttribute(k_network_inference_tc<FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+		k_network_inference_tc<FF><<<blocks, tc::kTileRows, smem, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); } while (0)
+		switch (c->feat_per_level) {
+			case 1: SNB_TC_TAP(1); break;
+			case 2: SNB_TC_TAP(2); break;
+			case 4: SNB_TC_TAP(4); break;
+			default: SNB_TC_TAP(8); break;
+		}
+#undef SNB_TC_TAP
+		SNB_LAUNCHED(c);
+		return SNB_OK;
+	}
 	const uint64_t tiles = (n + 31) / 32;
 	const int blocks = (int)std::min<uint64_t>((tiles + kFusedWarps - 1) / kFusedWarps, (uint64_t)c->sm_count * 8);
 	switch (c->feat_per_level) {

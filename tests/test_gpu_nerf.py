@@ -56,10 +56,13 @@ def test_march_samples_bit_exact(snb, orc, ctx, kind, w, h, spp, snap):
     np.testing.assert_array_equal(dt.cpu().numpy().view(np.uint32), rdt.view(np.uint32))
 
 
+@pytest.mark.parametrize("mlp", ["mma", "tc"])
 @pytest.mark.parametrize("kind", ["small16x2", "fox8x4", "f1", "f8", "big16x2"])
-def test_network_hash_indices_and_outputs(snb, orc, ctx, kind):
+def test_network_hash_indices_and_outputs(snb, orc, ctx, kind, mlp):
+    """mlp = "mma": warp-level mma.sync evaluator; "tc": CTA-level tcgen05/TMEM evaluator (128-row tiles, ragged last tile)."""
     m = common.model(kind)
     d = set_model(snb, ctx, m)
+    assert snb.snb_set_option(ctx, b"mlp", mlp.encode()) == 0
     n = 3000 + 7   # ragged: not a multiple of the 32-row tile
     rng = np.random.default_rng(5)
     coords = np.zeros((n, 7), np.float32)
@@ -68,8 +71,10 @@ def test_network_hash_indices_and_outputs(snb, orc, ctx, kind):
     L = m.n_levels
     dc = torch.from_numpy(coords).cuda()
     out, feat, hidx = dev((n, 4), torch.float16), dev((n, 32), torch.float16), dev((n, L * 8), torch.int32)
-    assert snb.snb_network_inference(ctx, dc.data_ptr(), n, out.data_ptr(), feat.data_ptr(), hidx.data_ptr()) == 0, snb.snb_last_error(ctx)
-    assert snb.snb_sync(ctx) == 0
+    rc = snb.snb_network_inference(ctx, dc.data_ptr(), n, out.data_ptr(), feat.data_ptr(), hidx.data_ptr())
+    snb.snb_set_option(ctx, b"mlp", b"mma")
+    assert rc == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0, snb.snb_last_error(ctx)
     rout, rfeat, rh = np.zeros((n, 4), np.uint16), np.zeros((n, 32), np.uint16), np.zeros((n, L * 8), np.uint32)
     orc.orc_network_inference(C.byref(d), O.P(coords), n, O.P(rout, O.pu16), O.P(rfeat, O.pu16), O.P(rh, O.pu32))
     np.testing.assert_array_equal(hidx.cpu().numpy().view(np.uint32), rh)                                   # hash indices: bit-exact
