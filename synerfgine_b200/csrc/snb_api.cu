@@ -48,6 +48,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		if (v == "mma") c->mlp_variant = 0;
 		else if (v == "tc") c->mlp_variant = 1;
 		else return c->fail(SNB_ERR_ARG, "mlp: expected mma | tc");
+	} else if (k == "overlap") {
+		c->overlap_layers = v != "0";
 	} else return c->fail(SNB_ERR_ARG, "unknown option");
 	return SNB_OK;
 }
@@ -69,6 +71,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	c->sm_count = prop.multiProcessorCount;
 	if (const char* mv = getenv("SNB_MARCH")) snb_set_option(c, "march", mv);
 	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
+	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
 	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
@@ -87,6 +90,7 @@ void snb_destroy(snb_ctx* c) {
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
 	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
 }

@@ -67,14 +67,20 @@ struct snb_ctx {
 	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
-	int march_variant = 4;             // 4 = ray-pool kernel (snb_pool_kernel.cuh); 3 = one ray per lane (SNB_MARCH=v3, A/B only)
+	int march_variant = 3;             // 4 = ray-pool kernel (snb_pool_kernel.cuh); 3 = one ray per lane (SNB_MARCH=v3, A/B only)
 
 	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)
 	static const int kStages = 5;   // 0 nerf raygen, 1 nerf fused march, 2 nerf normals+shadows, 3 mesh layer, 4 overlay
 	cudaEvent_t ev[kStages][2] = {};
 	bool ev_set[kStages] = {};
-	void stage_begin(int s) { if (!ev[s][0]) { cudaEventCreate(&ev[s][0]); cudaEventCreate(&ev[s][1]); } cudaEventRecord(ev[s][0], stream); ev_set[s] = false; }
-	void stage_end(int s) { cudaEventRecord(ev[s][1], stream); ev_set[s] = true; }
+	void stage_begin(int s, cudaStream_t st = nullptr) { if (!ev[s][0]) { cudaEventCreate(&ev[s][0]); cudaEventCreate(&ev[s][1]); } cudaEventRecord(ev[s][0], st ? st : stream); ev_set[s] = false; }
+	void stage_end(int s, cudaStream_t st = nullptr) { cudaEventRecord(ev[s][1], st ? st : stream); ev_set[s] = true; }
+
+	// second stream for the mesh layer of snb_frame: it does not depend on the NeRF layer until the overlay, and both are
+	// latency-bound, so they run concurrently (the reference serialises them with host syncs, engine.cu:386-406)
+	cudaStream_t stream2 = nullptr;
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	bool overlap_layers = true;
 
 	int fail(int code, const std::string& msg) { err = msg; return code; }
 	int cuda_fail(cudaError_t e, const char* what) {

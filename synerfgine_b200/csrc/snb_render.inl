@@ -99,7 +99,8 @@ static RtParams make_rt(const snb_rt_params* rt) {
 }
 
 // Mesh layer into the context's syn buffers (tile-sized).
-static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt) {
+static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, cudaStream_t st = nullptr) {
+	if (!st) st = c->stream;
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	if (rt->samples == 0 || rt->bounces == 0 || rt->shadow_iters == 0) return c->fail(SNB_ERR_ARG, "samples, bounces and shadow_iters must be >= 1");
 	const uint32_t n = (uint32_t)(dv.tw * dv.th);
@@ -109,16 +110,16 @@ static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* 
 	SNB_CUDA(c, c->d_syn_rgba.reserve((size_t)n * 16));
 	SNB_CUDA(c, c->d_syn_depth.reserve((size_t)n * 4));
 	const dim3 grid2((dv.tw + 15) / 16, (dv.th + 7) / 8);
-	c->stage_begin(3);
+	c->stage_begin(3, st);
 	if (c->syn_reset) {
-		k_syn_raygen<<<grid2, 128, 0, c->stream>>>(dv, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), nullptr, nullptr, c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
+		k_syn_raygen<<<grid2, 128, 0, st>>>(dv, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), nullptr, nullptr, c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
 		SNB_LAUNCHED(c);
 		c->syn_reset = false;
 	}
-	k_raytrace<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
+	k_raytrace<<<(n + 127) / 128, 128, 0, st>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
 	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
 	SNB_LAUNCHED(c);
-	c->stage_end(3);
+	c->stage_end(3, st);
 	return SNB_OK;
 }
 
@@ -228,8 +229,19 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 	const DevView nerf = nerf_view_of(syn, scale);
 	const size_t n_nerf = (size_t)nerf.tw * nerf.th;
 	rc = ensure_rng(c, syn, nerf); if (rc) return rc;
-	// 1. mesh layer (RayTracer::render)
-	rc = render_syn_layer(c, syn, rt); if (rc) return rc;
+	// 1. mesh layer (RayTracer::render) — forked onto the second stream, joined before the overlay
+	const bool fork = c->overlap_layers && rt->show_nerf;
+	if (fork) {
+		if (!c->stream2) {
+			SNB_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+		}
+		SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+		SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+	}
+	rc = render_syn_layer(c, syn, rt, fork ? c->stream2 : c->stream); if (rc) return rc;
+	if (fork) SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
 	// 2. NeRF layer with mesh shadows (Testbed::render sng overload)
 	SNB_CUDA(c, c->d_nerf_fb.reserve(n_nerf * 16));
 	SNB_CUDA(c, c->d_nerf_depth.reserve(n_nerf * 4));
@@ -239,6 +251,7 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 		rc = render_nerf_layer(c, nerf, true, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), c->d_positions.as<float>()); if (rc) return rc;
 		rc = nerf_post(c, nerf, rt, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_positions.as<float>(), c->d_normals.as<float>()); if (rc) return rc;
 	}
+	if (fork) SNB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
 	// 3. overlay (RayTracer::overlay), output colour space sRGB (engine.cu:406)
 	return snb_overlay(c, syn.tw, syn.th, rt, c->d_syn_rgba.as<float>(), c->d_syn_depth.as<float>(), c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), out_rgba, out_depth);
 }
