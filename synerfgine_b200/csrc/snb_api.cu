@@ -43,7 +43,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 	if (k == "march") {
 		if (v == "v3" || v == "lane") c->march_variant = 3;
 		else if (v == "v4" || v == "pool") c->march_variant = 4;
-		else return c->fail(SNB_ERR_ARG, "march: expected lane | pool");
+		else if (v == "tc") c->march_variant = 5;
+		else return c->fail(SNB_ERR_ARG, "march: expected lane | pool | tc");
 	} else if (k == "mlp") {
 		if (v == "mma") c->mlp_variant = 0;
 		else if (v == "tc") c->mlp_variant = 1;

@@ -13,6 +13,7 @@
 #include "snb_nerf_kernels.cuh"
 #include "snb_pool_kernel.cuh"
 #include "snb_mlp_tc.cuh"
+#include "snb_march_tc_kernel.cuh"
 #include "snb_sng_kernels.cuh"
 
 namespace snb {
@@ -67,7 +68,7 @@ struct snb_ctx {
 	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
-	int march_variant = 3;             // 4 = ray-pool kernel (snb_pool_kernel.cuh); 3 = one ray per lane (SNB_MARCH=v3, A/B only)
+	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused), 4 = ray pool (snb_pool_kernel.cuh), 5 = tcgen05 MLPs (snb_march_tc_kernel.cuh)
 
 	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)
 	static const int kStages = 5;   // 0 nerf raygen, 1 nerf fused march, 2 nerf normals+shadows, 3 mesh layer, 4 overlay

@@ -216,6 +216,88 @@ SNB_D uint2 cta_network_eval(CtaMlp& m) {
 	return r;
 }
 
+// ---- compact form for the march kernel: ONE 16 KB operand buffer and 64 TMEM columns per CTA ---------------------------------
+// Every layer's output overwrites the operand buffer only after the MMA that read it has completed (await_layer), and every
+// accumulator lives at columns 0..63 because layer i+1's MMA is issued only after all threads pulled layer i out of TMEM.
+constexpr uint32_t kTmemColsCompact = 64;
+constexpr int kCompactW = 0;                                   // 20480 B weights
+constexpr int kCompactBuf = kMlpHalves * 2;                    // 16384 B operand buffer ([128 x 32] or [128 x 64])
+constexpr int kCompactBar = kCompactBuf + kTileRows * 64 * 2;  // mbarriers + TMEM address
+constexpr int kCompactBytes = kCompactBar + 32;
+
+SNB_D void cta_mlp_init_compact(CtaMlp& m, unsigned char* smem, const __half* __restrict__ w_umma_global) {
+	m.smem = smem;
+	m.bar_w = smem_u32(smem + kCompactBar);
+	m.bar_mma = smem_u32(smem + kCompactBar + 8);
+	m.phase = 0;
+	const int tid = threadIdx.x;
+	if (tid == 0) { mbar_init(m.bar_w, 1); mbar_init(m.bar_mma, 1); mbar_fence_init(); }
+	if (tid < 32) tmem_alloc(smem_u32(smem + kCompactBar + 16), kTmemColsCompact);
+	fence_before_sync();
+	__syncthreads();
+	fence_after_sync();
+	m.tmem = *reinterpret_cast<volatile uint32_t*>(smem + kCompactBar + 16);
+	if (tid == 0) {
+		mbar_expect_tx(m.bar_w, kMlpHalves * 2);
+		tma_bulk_g2s(smem_u32(smem + kCompactW), w_umma_global, kMlpHalves * 2, m.bar_w);
+	}
+	mbar_wait(m.bar_w, 0);
+}
+SNB_D void cta_mlp_free_compact(CtaMlp& m) {
+	fence_before_sync();
+	__syncthreads();
+	if (threadIdx.x < 32) tmem_dealloc(m.tmem, kTmemColsCompact);
+}
+
+// Precondition: every thread wrote its 32 feature halves into the buffer in the [128 x 32] layout (chunk_offset<32>(row, 0..3)).
+// sh = this row's 16 SH halves. Returns {r, g, b, sigma} raw fp16 network outputs. All 128 threads must call it.
+SNB_D uint2 cta_network_eval_compact(CtaMlp& m, const uint32_t (&sh)[8]) {
+	const int row = threadIdx.x;
+	const bool issuer = threadIdx.x == 0;
+	const uint32_t lane_base = m.tmem + ((uint32_t)(row & ~31) << 16);
+	unsigned char* buf = m.smem + kCompactBuf;
+	const uint32_t sW = smem_u32(m.smem + kCompactW), sBuf = smem_u32(buf);
+	publish_operand();                                                                  // density 32 -> 64, ReLU
+	if (issuer) { fence_after_sync(); issue_layer<32, 64>(m.tmem, sBuf, sW + kOffDW1 * 2, m.bar_mma); }
+	await_layer(m);
+	hidden_to_smem(lane_base, buf, row);
+	publish_operand();                                                                  // density 64 -> 16
+	if (issuer) { fence_after_sync(); issue_layer<64, 16>(m.tmem, sBuf, sW + kOffDW2 * 2, m.bar_mma); }
+	await_layer(m);
+	uint32_t sigma_bits;
+	{
+		uint32_t v[16];
+		tmem_ld16(lane_base, v);
+		tmem_wait_ld();
+		uint32_t p[8];
+#pragma unroll
+		for (int i = 0; i < 8; ++i) p[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), false);
+		sigma_bits = p[0] & 0xFFFFu;
+		*reinterpret_cast<uint4*>(buf + chunk_offset<32>(row, 0)) = make_uint4(p[0], p[1], p[2], p[3]);
+		*reinterpret_cast<uint4*>(buf + chunk_offset<32>(row, 1)) = make_uint4(p[4], p[5], p[6], p[7]);
+		*reinterpret_cast<uint4*>(buf + chunk_offset<32>(row, 2)) = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+		*reinterpret_cast<uint4*>(buf + chunk_offset<32>(row, 3)) = make_uint4(sh[4], sh[5], sh[6], sh[7]);
+	}
+	publish_operand();                                                                  // rgb [16 | 16 SH] -> 64, ReLU
+	if (issuer) { fence_after_sync(); issue_layer<32, 64>(m.tmem, sBuf, sW + kOffRW1 * 2, m.bar_mma); }
+	await_layer(m);
+	hidden_to_smem(lane_base, buf, row);
+	publish_operand();                                                                  // rgb 64 -> 64, ReLU
+	if (issuer) { fence_after_sync(); issue_layer<64, 64>(m.tmem, sBuf, sW + kOffRW2 * 2, m.bar_mma); }
+	await_layer(m);
+	hidden_to_smem(lane_base, buf, row);
+	publish_operand();                                                                  // rgb 64 -> 16 (3 live)
+	if (issuer) { fence_after_sync(); issue_layer<64, 16>(m.tmem, sBuf, sW + kOffRW3 * 2, m.bar_mma); }
+	await_layer(m);
+	uint32_t v[4];
+	tmem_ld4(lane_base, v);
+	tmem_wait_ld();
+	uint2 r;
+	r.x = h22u(__floats2half2_rn(__uint_as_float(v[0]), __uint_as_float(v[1])));
+	r.y = (uint32_t)__half_as_ushort(__float2half_rn(__uint_as_float(v[2]))) | (sigma_bits << 16);
+	return r;
+}
+
 } // namespace tc
 
 // NerfNetwork inference on explicit NerfCoordinates (n x 7 floats) through the tcgen05 evaluator: the parity tap of the

@@ -34,6 +34,22 @@ static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int r
 		SNB_LAUNCHED(c);
 		return SNB_OK;
 	}
+	if (c->march_variant == 5) {   // MLPs on tcgen05 tensor cores
+		static int per_sm = 0;
+		if (per_sm == 0) {
+			SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_tc<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
+			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_tc<F, ALT>, tc::kTileRows, kTcSmemBytes));
+			// registers (96) and shared memory (39 KB) allow 5 CTAs / SM (ncu launch__occupancy_limit_*); the occupancy query
+			// answered < 2 for this kernel on driver 580.159, so fall back to the limits known from the build. TMEM: 512 columns / SM.
+			if (per_sm < 2) per_sm = 5;
+			per_sm = std::max(1, std::min(per_sm, (int)(512 / tc::kTmemColsCompact)));
+		}
+		c->fused_blocks_per_sm = per_sm;
+		const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + tc::kTileRows - 1) / tc::kTileRows));
+		k_nerf_march_tc<F, ALT><<<blocks, tc::kTileRows, kTcSmemBytes, c->stream>>>(c->model, dv, out, render_mode, c->d_queue.as<RayRec>(), qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+		SNB_LAUNCHED(c);
+		return SNB_OK;
+	}
 	static int per_sm = 0;
 	if (per_sm == 0) {
 		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_pool<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PoolSmem)));

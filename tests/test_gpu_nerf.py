@@ -87,9 +87,12 @@ def test_network_hash_indices_and_outputs(snb, orc, ctx, kind, mlp):
 
 
 @pytest.mark.parametrize("kind,alt,w,h", [("small16x2", 0, 128, 96), ("small16x2", 1, 128, 96), ("fox8x4", 1, 64, 64), ("unit16x2", 0, 64, 64), ("big16x2", 1, 64, 64)])
-def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h):
+@pytest.mark.parametrize("march", ["lane", "pool", "tc"])
+def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
+    """march: "lane" = one ray per lane + mma.sync MLPs, "pool" = warp ray pool, "tc" = MLPs on tcgen05/TMEM (CTA level)."""
     m = common.model(kind)
     d = set_model(snb, ctx, m)
+    assert snb.snb_set_option(ctx, b"march", march.encode()) == 0
     cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
     v = common.make_view(w, h, cam=cam)
     fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
@@ -100,7 +103,9 @@ def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h):
     else:
         rc = snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr())
     assert rc == 0, snb.snb_last_error(ctx)
-    assert snb.snb_sync(ctx) == 0
+    rc = snb.snb_sync(ctx)
+    snb.snb_set_option(ctx, b"march", b"lane")
+    assert rc == 0, snb.snb_last_error(ctx)
     rfb, rdepth, rpos, ns = O.render_nerf(d, v, alt, positions=bool(alt))
     a = fb.cpu().numpy()
     assert (rfb[..., 3] > 0.5).mean() > 0.05, "degenerate test: nothing visible"
