@@ -125,6 +125,22 @@ SNB_HD float advance_past_voxel(float t, const Stepping& s, v3 pos, v3 dir, v3 i
 	return from_step_space(t + ceilf(fmaxf(t_target - t, 0.5f)), s);
 }
 
+#ifdef __CUDACC__
+// Out-of-line twins for the persistent march kernel: its loop inlined to_step_space three times and from_step_space
+// twice (~500 SASS instructions) and no longer fitted the instruction cache (profiles/r01_ncu_fused_v3.md). Same
+// arithmetic, one copy of the code.
+__device__ __noinline__ float to_step_space_call(float t, Stepping s) { return to_step_space(t, s); }
+__device__ __noinline__ float from_step_space_call(float n, Stepping s) { return from_step_space(n, s); }
+__device__ __forceinline__ float step_size_call(float t, const Stepping& s) { return from_step_space_call(to_step_space_call(t, s) + 1.0f, s) - t; }
+__device__ __forceinline__ float advance_past_voxel_call(float t, const Stepping& s, v3 pos, v3 dir, v3 idir, uint32_t mip) {
+	const float res = (float)kGridSize * pow2i(-(int)mip), inv_res = pow2i((int)mip) * (1.0f / (float)kGridSize);
+	float t_target = t + voxel_exit_distance(pos, dir, idir, res, inv_res);
+	t = to_step_space_call(t, s);
+	t_target = to_step_space_call(t_target, s);
+	return from_step_space_call(t + ceilf(fmaxf(t_target - t, 0.5f)), s);
+}
+#endif
+
 SNB_HD uint32_t mip_of(v3 pos, uint32_t max_cascade = kCascades - 1) {
 	// frexpf exponent from the exponent field; zero / subnormal inputs give a negative m either way and clamp to 0
 	const float maxval = vmax(vabs(pos - 0.5f));

@@ -185,11 +185,6 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	int k = 0, n_empty = 0;
 	bool alive = false, drained = false;
 	float max_weight = 0.0f;
-	uint32_t sh_frag[2][4];
-#pragma unroll
-	for (int m = 0; m < 2; ++m)
-#pragma unroll
-		for (int i = 0; i < 4; ++i) sh_frag[m][i] = 0u;
 	{ // zero the whole row once so never-filled rows hold finite values
 		uint4* row = reinterpret_cast<uint4*>(tile + lane * kTileStrideH);
 #pragma unroll
@@ -204,7 +199,9 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth); ++n_hits; }
 	};
 
+	bool fin = false;   // ray ended in the previous iteration: one finish() site keeps the loop small
 	for (;;) {
+		if (fin) { finish(); fin = false; }
 		// -- refill empty slots: one atomic per warp -----------------------------------------------------------------
 		const unsigned int need = __ballot_sync(0xFFFFFFFFu, !alive);
 		if (need && !drained) {
@@ -224,8 +221,6 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				stage_sh_row(tile, lane, sh);
 			}
 			if (base + __popc(need) >= n_rays) drained = true;
-			__syncwarp();
-			load_sh_frags(tile, lane, sh_frag);
 		}
 		if (__ballot_sync(0xFFFFFFFFu, alive) == 0) break;
 
@@ -237,14 +232,14 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			for (;;) {
 				if (searching) {
 					const v3 pos = o + d * t;
-					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { finish(); searching = false; }   // left the volume
+					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { fin = true; searching = false; }   // left the volume
 					else {
 						uint32_t mip = clamp_mip(mip_of(pos), env);
 						if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) { valid = true; searching = false; n_empty = 0; }
-						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { finish(); searching = false; }
+						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { fin = true; searching = false; }
 						else {
 							while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
-							t = advance_past_voxel(t, env.st, pos, d, idir, mip);
+							t = advance_past_voxel_call(t, env.st, pos, d, idir, mip);
 						}
 					}
 				}
@@ -258,7 +253,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		v3 wpos = mk3(0, 0, 0);
 		float wdt = 0.0f;
 		if (valid) {
-			const float dt = step_size(t, env.st);
+			const float dt = step_size_call(t, env.st);
 			wpos = (o + d * t - model.train_aabb.lo) / aabb_diag;   // warp_position
 			wdt = dt_warp(dt);
 			t += dt;
@@ -266,7 +261,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			encode_position_to_row<F, false>(s_levels, wpos, tile + lane * kTileStrideH, nullptr);
 		}
 		// -- both MLPs ---------------------------------------------------------------------------------------------------
-		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, sh_frag);
+		const uint2 net = warp_network_eval_rolled(s_w, tile, out_tile, lane);
 
 		// -- composite -------------------------------------------------------------------------------------------------
 		if (valid) {
@@ -293,7 +288,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			if (rgba.w > (1.0f - model.min_transmittance)) {
 				const float inv_a = 1.0f / rgba.w;
 				rgba.x *= inv_a; rgba.y *= inv_a; rgba.z *= inv_a; rgba.w *= inv_a;
-				finish();
+				fin = true;
 			} else if (++k == kBatchSteps) {
 				// batch boundary: the sng compositor rewinds t to the last composited sample
 				if (ALT) t = depth / dot(cam_fwd, d);

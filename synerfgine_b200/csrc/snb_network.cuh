@@ -368,6 +368,82 @@ SNB_D uint2 warp_network_eval(const uint32_t* __restrict__ smem_w, __half* tile,
 	return r;
 }
 
+// The same network with the two 16-row m-tiles evaluated one after the other in a rolled loop: half the code of
+// warp_network_eval (the persistent march kernel has to stay inside the 32 KB instruction cache, see
+// profiles/r01_ncu_fused_v3.md) and half the live fragments; weight fragments are fetched twice instead. The SH block is read
+// from the staged row (k-tile 2) instead of being carried in registers. Bit-identical results (same mma order per row).
+template <int KT_IN, int KT_OUT, bool RELU, bool GLOBAL_W>
+SNB_D void dense_to_frags_1m(const uint32_t* __restrict__ wfrag, int lane, const uint32_t (&a)[KT_IN][4], uint32_t (&out)[KT_OUT][4]) {
+#pragma unroll
+	for (int ko = 0; ko < KT_OUT; ++ko) {
+		float acc[2][4];
+#pragma unroll
+		for (int h = 0; h < 2; ++h)
+#pragma unroll
+			for (int i = 0; i < 4; ++i) acc[h][i] = 0.0f;
+#pragma unroll
+		for (int h = 0; h < 2; ++h) {
+			const int nt = 2 * ko + h;
+#pragma unroll
+			for (int kt = 0; kt < KT_IN; ++kt) {
+				const uint2 b = load_wfrag<GLOBAL_W>(wfrag + ((nt * KT_IN + kt) * 32 + lane) * 2);
+				mma16816(acc[h], a[kt], b.x, b.y);
+			}
+		}
+		out[ko][0] = pack_relu_h2(acc[0][0], acc[0][1], RELU);
+		out[ko][1] = pack_relu_h2(acc[0][2], acc[0][3], RELU);
+		out[ko][2] = pack_relu_h2(acc[1][0], acc[1][1], RELU);
+		out[ko][3] = pack_relu_h2(acc[1][2], acc[1][3], RELU);
+	}
+}
+
+template <bool GLOBAL_W = false>
+SNB_D uint2 warp_network_eval_rolled(const uint32_t* __restrict__ smem_w, __half* tile, __half* out_tile, int lane) {
+	__syncwarp();
+	const int g = lane >> 2, t = lane & 3;
+	uint32_t* o32 = reinterpret_cast<uint32_t*>(out_tile);
+#pragma unroll 1
+	for (int m = 0; m < 2; ++m) {
+		const __half* rows = tile + (16 * m + (lane & 7) + ((lane >> 3) & 1) * 8) * kTileStrideH + (lane >> 4) * 8;
+		uint32_t a_feat[2][4];
+		ldmatrix_x4(a_feat[0], rows);
+		ldmatrix_x4(a_feat[1], rows + 16);
+		uint32_t h1[4][4];
+		dense_to_frags_1m<2, 4, true, GLOBAL_W>(smem_w + kFragDW1, lane, a_feat, h1);       // 32 -> 64, ReLU
+		uint32_t rgb_in[2][4];
+		{
+			uint32_t dens[1][4];
+			dense_to_frags_1m<4, 1, false, GLOBAL_W>(smem_w + kFragDW2, lane, h1, dens);     // 64 -> 16
+#pragma unroll
+			for (int i = 0; i < 4; ++i) rgb_in[0][i] = dens[0][i];
+		}
+		ldmatrix_x4(rgb_in[1], rows + kTileShCol);                                        // SH block of the rows
+		uint32_t g1[4][4];
+		dense_to_frags_1m<2, 4, true, GLOBAL_W>(smem_w + kFragRW1, lane, rgb_in, g1);       // 32 -> 64, ReLU
+		uint32_t g2[4][4];
+		dense_to_frags_1m<4, 4, true, GLOBAL_W>(smem_w + kFragRW2, lane, g1, g2);           // 64 -> 64, ReLU
+		float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+		for (int kt = 0; kt < 4; ++kt) {
+			const uint2 b = load_wfrag<GLOBAL_W>(smem_w + kFragRW3 + (kt * 32 + lane) * 2);
+			mma16816(acc, g2[kt], b.x, b.y);
+		}
+		if (t == 0) {
+			o32[(16 * m + g) * 2] = h22u(__floats2half2_rn(acc[0], acc[1]));
+			o32[(16 * m + g + 8) * 2] = h22u(__floats2half2_rn(acc[2], acc[3]));
+			reinterpret_cast<unsigned short*>(o32)[(16 * m + g) * 4 + 3] = (unsigned short)(rgb_in[0][0] & 0xFFFFu);
+			reinterpret_cast<unsigned short*>(o32)[(16 * m + g + 8) * 4 + 3] = (unsigned short)(rgb_in[0][1] & 0xFFFFu);
+		} else if (t == 1) {
+			reinterpret_cast<__half*>(o32)[(16 * m + g) * 4 + 2] = __float2half_rn(acc[0]);
+			reinterpret_cast<__half*>(o32)[(16 * m + g + 8) * 4 + 2] = __float2half_rn(acc[2]);
+		}
+	}
+	__syncwarp();
+	const uint2 r = *reinterpret_cast<const uint2*>(o32 + lane * 2);
+	__syncwarp();
+	return r;
+}
+
 // SH block of the staging tile: a lane (re)writes its row when its slot receives a new ray ...
 SNB_D void stage_sh_row(__half* tile, int lane, const uint32_t (&sh)[8]) {
 	uint4* dst = reinterpret_cast<uint4*>(tile + lane * kTileStrideH + kTileShCol);
