@@ -153,9 +153,12 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 // empty space take DDA steps until at least kMinFill lanes hold a sample position (lanes that already have one
 // wait), (3) encode + both MLPs for the lanes that have a sample, (4) composite. A lane still searching after (2)
 // simply carries on in the next iteration, so one ray crossing a long empty gap no longer stalls the other 31.
+#ifndef SNB_LANE_CTAS
+#define SNB_LANE_CTAS 4     // resident CTAs per SM the register budget is set for (tuning hook)
+#endif
 constexpr int kMinFill = 26;
 template <int F, bool ALT>
-__global__ void __launch_bounds__(kFusedThreads, 4)
+__global__ void __launch_bounds__(kFusedThreads, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
                    unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
 	__shared__ __align__(16) uint32_t s_w[kFragWords];

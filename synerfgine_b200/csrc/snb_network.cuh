@@ -175,7 +175,7 @@ SNB_D void level_blend(const typename FeatVec<F>::T (&vals)[8], const LevelFrac&
 // feature-minor, as the reference's AoS row). Levels are processed in groups of G: all 8*G gathers of a group are issued
 // before the first one is consumed, so a sample pays L/G dependent L2 round trips instead of L (with in-order issue a plain
 // unrolled loop serialises them: each level's HFMA chain blocks the next level's loads). The group loop itself is not
-// unrolled: the march kernel's hot loop has to stay inside the instruction cache (profiles/r01_ncu_fused_v2.md).
+// unrolled: the march kernel's hot loop has to stay inside the instruction cache (profiles/r01_ncu_fused_v2.md, r01_ncu_fused_v3.md).
 // CS = byte stride between consecutive 16-byte chunks (8 halves) of the row: 16 for a plain row-major tile, 128 for the
 // tcgen05 K-major core-matrix layout (snb_mlp_tc.cuh).
 template <int F, bool TAP, int CS = 16>

@@ -5,7 +5,7 @@
 // :577-788 / composite_kernel_nerf_alt :476-575, extract_from_payload :1578-1612, shade_kernel_nerf :1788-1828 and the host
 // loops NerfTracer::trace / trace_alt :2128-2401.
 //
-// Why a pool (profiles/r01_ncu_fused_v3.md, r01_ncu_pool_v4.md): with one ray per lane the empty-space DDA ran with 2-5 of 32
+// Why a pool (profiles/r01_ncu_fused_v3.md): with one ray per lane the empty-space DDA ran with 2-5 of 32
 // lanes active and was ~35 % of all issued instructions although it is only ~0.5 DDA steps per network sample. A CTA-wide
 // pool with compacted lists fixed the packing but spent 44 % of its time in the two CTA barriers per iteration. This form
 // keeps warps autonomous (no barrier, no atomics on shared memory): every LANE owns kSlotsPerLane ray slots in shared memory
