@@ -56,6 +56,16 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"
 
 
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner) goes to stderr."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    def emit(line):
+        os.write(real, (line + "\n").encode())
+    return emit
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -152,6 +162,7 @@ def run_reference(args, rank, world):
 
 
 def run_ours(args, rank, local_rank, world):
+    emit = claim_stdout()
     import torch
     import torch.distributed as dist
     import common
@@ -169,21 +180,36 @@ def run_ours(args, rank, local_rank, world):
     eng = Engine()
     eng.set_virtual_world_json(scenes.scene_json(args.scene), scenes.mesh_dir())
     halo = tiles.halo_for(eng.rt.nerf_shadow_kernel, bool(eng.rt.show_shadow_on_nerf))
-    strip = tiles.strip_for(rank, world, W, halo, align=max(1, eng.rt.syn_px_scale))
-    x0, x1, hx0, hx1 = strip.x0, strip.x1, strip.hx0, strip.hx1
-    tile = Tile(hx0, 0, hx1 - hx0, H) if world > 1 else None
-    eng.init(W, H, tb, tile=tile)
+    align = max(1, eng.rt.syn_px_scale)
+    bal = tiles.StripBalancer(W, world, halo, align)       # starts from equal strips, moves the edges from measured frame times
+    strip = bal.strip(rank)
+    eng.init(W, H, tb, tile=Tile(strip.hx0, 0, strip.render_width, H) if world > 1 else None)
     lib, ctx = tb.lib, tb.ctx
     n_rays_total = W * H
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-    gather_buf = [torch.empty((H, W * (r + 1) // world - W * r // world, 4), device="cuda") for r in range(world)] if (world > 1 and rank == 0) else None
+    full_frame = torch.empty((H, W, 4), device="cuda") if (world > 1 and rank == 0) else None
+    ev_a = torch.cuda.Event(enable_timing=True); ev_b = torch.cuda.Event(enable_timing=True)
+    col_cost = torch.zeros(W, device="cuda", dtype=torch.float32) if world > 1 else None
 
     def one_frame():
         lib.snb_reset_accumulation(ctx)                   # accumulation reset before each timed frame
-        rgba, depth = eng.frame(sync=False)
-        if world > 1:
-            mine = rgba[:, x0 - hx0:x1 - hx0].contiguous()
-            dist.gather(mine, gather_buf, dst=0)           # framebuffer assembly over NVLink (NCCL), once per frame
+        if world == 1:
+            return eng.frame(sync=False)[0]
+        s = bal.strip(rank)
+        ev_a.record(stream)
+        rgba, depth = eng.frame(sync=False, tile=Tile(s.hx0, 0, s.render_width, H))
+        ev_b.record(stream)
+        mine = rgba[:, s.crop].contiguous()
+        tiles.assemble_on_root(mine, bal.bounds, rank, world, dist, full_frame)   # framebuffer assembly over NVLink (NCCL p2p), once per frame
+        if bal.due():                                     # strip edges follow the measured cost: one 7.7 KB all_reduce
+            hits = (mine[..., 3] > 0).sum(0, dtype=torch.float32)
+            wgt = hits + 0.05 * torch.clamp(hits.max(), min=1.0)
+            ev_b.synchronize()
+            col_cost.zero_()
+            col_cost[s.x0:s.x1] = wgt * (ev_a.elapsed_time(ev_b) / float(wgt.sum()))
+            dist.all_reduce(col_cost)
+            bal.observe(col_cost.cpu().numpy().astype(np.float64))
+        bal.tick()
         return rgba
 
     with torch.cuda.stream(stream):
@@ -223,7 +249,9 @@ def run_ours(args, rank, local_rank, world):
         eng_frame_host = eng.frame
         sc = eng.scene
         h2d = sc.n_objects * 72 + sc.n_materials * C.sizeof(type(sc.materials[0])) + sc.n_lights * C.sizeof(type(sc.lights[0])) + 96
-        tw = (hx1 - hx0) if world > 1 else W
+        strip = bal.strip(rank)
+        tile = Tile(strip.hx0, 0, strip.render_width, H) if world > 1 else None
+        tw = strip.render_width if world > 1 else W
         pin_rgba = torch.empty((H, tw, 4), dtype=torch.float32).pin_memory(); pin_depth = torch.empty((H, tw), dtype=torch.float32).pin_memory()
         d2h = pin_rgba.numel() * 4 + pin_depth.numel() * 4
 
@@ -260,7 +288,7 @@ def run_ours(args, rank, local_rank, world):
             "metric": "Mrays/s, 1080p NeRF+mesh+shadows", "value": n_rays_total * K / (total_ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wu,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32 march / f16 MLP (fp32 accumulate)", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "resolution": [W, H], "scene": args.scene, "parallelism": f"{world} column strips, halo {halo}px" if world > 1 else "single GPU",
+            "config": {"workload": WORKLOAD, "resolution": [W, H], "scene": args.scene, "parallelism": (f"{world} column strips, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves)" if world > 1 else "single GPU"),
                        "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples / K, "rays_marched_per_frame": rays / K, "march_stats_last_frame": march_stats,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()}},
             "e2e": {"value": n_rays_total * K / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / K * 1e3},
@@ -275,7 +303,7 @@ def run_ours(args, rank, local_rank, world):
             cw, ch = [int(x) for x in args.cpu_sample.split("x")]
             mrays, ms = cpu_oracle_rate(args.scene, cw, ch, 1, 1, 0)
             out["cpu_baseline"] = {"value": mrays, "unit": "Mrays/s", "cores": 1, "kind": "port", "sample": f"one {cw}x{ch} frame of the same scene/camera (oracle, scalar C++)", "ms": ms}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     tb.close()
     if world > 1:
         dist.destroy_process_group()

@@ -177,9 +177,15 @@ class Engine:
         self.rt.tonemap_curve = tb.tonemap_curve
         tb._check(tb.lib.snb_set_scene(tb.ctx, sc.objects, sc.n_objects, sc.materials, sc.n_materials, sc.lights, sc.n_lights), "snb_set_scene")
         tb._check(tb.lib.snb_seed_rng(tb.ctx, 1999), "snb_seed_rng")
-        w, h = (tile.w, tile.h) if tile is not None else (res_width, res_height)
-        self.out_rgba = torch.empty((h, w, 4), dtype=torch.float32, device=tb.device)
-        self.out_depth = torch.empty((h, w), dtype=torch.float32, device=tb.device)
+        # full-frame capacity once; a tile (which may change from frame to frame, tiles.StripBalancer) renders into a view of it
+        self._rgba_store = torch.empty(res_width * res_height * 4, dtype=torch.float32, device=tb.device)
+        self._depth_store = torch.empty(res_width * res_height, dtype=torch.float32, device=tb.device)
+        self._bind_outputs(tile)
+
+    def _bind_outputs(self, tile):
+        w, h = (tile.w, tile.h) if tile is not None else (self.width, self.height)
+        self.out_rgba = self._rgba_store[:h * w * 4].view(h, w, 4)
+        self.out_depth = self._depth_store[:h * w].view(h, w)
 
     def set_syn_samples(self, n):
         self.rt.shadow_iters = n
@@ -193,8 +199,12 @@ class Engine:
         sc.advance()
         tb._check(tb.lib.snb_update_scene(tb.ctx, sc.objects, sc.n_objects, sc.materials, sc.n_materials, sc.lights, sc.n_lights), "snb_update_scene")
 
-    def frame(self, sync=True, host=False):
+    def frame(self, sync=True, host=False, tile=None):
+        """One Engine::frame. `tile` (an _lib.Tile) replaces the tile given to init() from this frame on."""
         tb = self.testbed
+        if tile is not None and (self.tile is None or (tile.x0, tile.y0, tile.w, tile.h) != (self.tile.x0, self.tile.y0, self.tile.w, self.tile.h)):
+            self.tile = tile
+            self._bind_outputs(tile)
         v = tb.make_view(self.width, self.height, self.frame_index)
         tile_ref = C.byref(self.tile) if self.tile is not None else None
         if host:

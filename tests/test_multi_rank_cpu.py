@@ -126,3 +126,84 @@ def test_missing_halo_is_detected(tmp_path):
     seam = W // 2
     assert not np.array_equal(got[:, seam - 2:seam + 2], nrm[:, seam - 2:seam + 2, 0])
     np.testing.assert_array_equal(got[:, :seam - 2], nrm[:, :seam - 2, 0])
+
+
+# ---- load-balanced strips (tiles.StripBalancer): same frame, unequal strips, exact-size point-to-point assembly ----------
+
+def test_balanced_bounds_equalise_cost_and_respect_alignment():
+    rng = np.random.default_rng(7)
+    for width, align in ((1920, 1), (1920, 4), (64, 2)):
+        cost = rng.random(width) ** 4
+        cost[width // 3: width // 2] += 5.0                     # a heavy object off-centre
+        for world in (2, 3, 4, 8):
+            b = tiles.balanced_bounds(cost, world, align=align, min_width=2 * align)
+            assert b[0] == 0 and b[-1] == width and len(b) == world + 1
+            assert all(x % align == 0 for x in b) and all(y - x >= 2 * align for x, y in zip(b, b[1:]))
+            parts = [cost[x:y].sum() for x, y in zip(b, b[1:])]
+            equal = [cost[x:y].sum() for x, y in zip(range(0, width, width // world), range(width // world, width + 1, width // world))]
+            assert max(parts) <= max(equal) + 1e-9                  # never worse than equal strips
+            if width >= 1920:                                       # (narrow frames are dominated by the minimum strip width)
+                assert max(parts) <= cost.sum() / world + cost.max() * align + 1e-9   # within one aligned column group of ideal
+    # all cost in one column: every other strip still gets its minimum width
+    cost = np.zeros(40); cost[17] = 1.0
+    b = tiles.balanced_bounds(cost, 4, align=1, min_width=4)
+    assert all(y - x >= 4 for x, y in zip(b, b[1:])) and b[-1] == 40
+    with pytest.raises(ValueError):
+        tiles.balanced_bounds(np.ones(8), 4, align=1, min_width=4)
+
+
+def test_strip_balancer_hysteresis():
+    bal = tiles.StripBalancer(1920, 4, halo=4)
+    assert bal.bounds == [0, 480, 960, 1440, 1920] and bal.min_width == 8
+    flat = np.ones(1920)
+    assert not bal.observe(flat) and bal.changes == 0              # already balanced: edges stay
+    heavy = np.full(1920, 0.01); heavy[700:1200] = 1.0
+    assert bal.observe(heavy) and bal.changes == 1
+    before = list(bal.bounds)
+    assert not bal.observe(heavy * 1.01) and bal.bounds == before  # same profile again: no further move
+    s = bal.strip(1)
+    assert (s.x0, s.x1) == (bal.bounds[1], bal.bounds[2]) and s.hx0 == s.x0 - 4 and s.hx1 == s.x1 + 4
+    c = tiles.column_cost_of_strip(s, 1920, 3.0, np.arange(s.width))
+    assert abs(c.sum() - 3.0) < 1e-9 and c[:s.x0].sum() == 0 and c[s.x1:].sum() == 0
+
+
+def _worker_balanced(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        m = common.model("small16x2")
+        v = common.make_view(W, H)
+        render_tile = make_tile_renderer(m.desc(), v)
+        bal = tiles.StripBalancer(W, world, tiles.halo_for(1))
+        frames = []
+        for it in range(3):                                        # frame 0 on equal strips, then on re-balanced ones
+            s = bal.strip(rank)
+            rgba, depth = render_tile(s.hx0, 0, s.render_width, H)
+            mine = torch.cat([rgba[:, s.crop, :], depth[:, s.crop, None]], dim=2).contiguous()
+            full = tiles.assemble_on_root(mine, bal.bounds, rank, world, dist)
+            hits = (mine[..., 3] != 0).sum(0).numpy()
+            # synthetic "frame time": proportional to the hits of the strip, so the split must move towards the object
+            cost = torch.from_numpy(tiles.column_cost_of_strip(s, W, 1.0 + float(hits.sum()), hits))
+            dist.all_reduce(cost)
+            bal.observe(cost.numpy())
+            if rank == 0:
+                frames.append(full.numpy())
+        if rank == 0:
+            np.savez(out_path, frames=np.stack(frames), bounds=np.array(bal.bounds), changes=bal.changes)
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_rebalanced_strips_give_the_same_frame(tmp_path, world):
+    m = common.model("small16x2")
+    v = common.make_view(W, H)
+    fb, depth, pos, nrm = oracle_nerf_layer(m.desc(), v)
+    expect = np.concatenate([fb[..., :3], nrm[..., :1], depth[..., None]], axis=2)
+    out = str(tmp_path / "balanced.npz")
+    mp.spawn(_worker_balanced, args=(world, _free_port(), out), nprocs=world, join=True)
+    got = np.load(out)
+    for f in got["frames"]:                                        # every frame, whatever the split, is the single-rank frame
+        np.testing.assert_array_equal(f.view(np.uint32), expect.view(np.uint32))
+    assert list(got["bounds"])[0] == 0 and list(got["bounds"])[-1] == W
