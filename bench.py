@@ -173,6 +173,8 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     W, H, K, Wu = args.width, args.height, args.steps, max(3, args.warmup)
+    if world > 1:
+        Wu = max(Wu, 10)                                  # the strip edges settle during warm-up (tiles.StripBalancer); reported as `warmup`
     stream = torch.cuda.Stream()
     tb = Testbed(local_rank, stream=stream)
     model = common.model("fox16x2")
@@ -208,7 +210,10 @@ def run_ours(args, rank, local_rank, world):
             col_cost.zero_()
             col_cost[s.x0:s.x1] = wgt * (ev_a.elapsed_time(ev_b) / float(wgt.sum()))
             dist.all_reduce(col_cost)
-            bal.observe(col_cost.cpu().numpy().astype(np.float64))
+            t_ms = ev_a.elapsed_time(ev_b)
+            moved = bal.observe(col_cost.cpu().numpy().astype(np.float64))
+            if os.environ.get("SNB_BENCH_DEBUG"):
+                print(f"[balance] frame {bal.frames} rank {rank} strip {s.x0}-{s.x1} render {t_ms:.3f} ms moved={moved} -> {bal.bounds}", file=sys.stderr)
         bal.tick()
         return rgba
 

@@ -126,25 +126,29 @@ def strip_from_bounds(bounds, rank, width, halo, align=1):
 
 class StripBalancer:
     """Per-frame feedback on the strip edges. `observe(col_cost)` takes the GLOBAL per-column cost (already all-reduced) and
-    moves the edges only when the predicted slowest strip gets at least `gain` (default 5 %) faster — a partition change
-    re-seeds the per-pixel RNG states and may grow buffers, so it must stay rare once the split has settled."""
+    moves the edges only when the predicted slowest strip gets at least `gain` (default 8 %) faster — a partition change
+    re-seeds the per-pixel RNG states and may grow buffers, so it must stay rare once the split has settled. The frame that
+    follows a move pays for exactly that and is therefore not used as a measurement (`due()` is False for it)."""
 
-    def __init__(self, width, world, halo, align=1, gain=0.05):
+    def __init__(self, width, world, halo, align=1, gain=0.08):
         self.width, self.world, self.halo, self.align, self.gain = width, world, halo, align, gain
         self.min_width = max(align, 2 * (-(-halo // align) * align))
         self.bounds = [strip_for(r, world, width, halo, align).x0 for r in range(world)] + [width]
         self.frames = 0
         self.changes = 0
+        self.cooldown = 0
 
     def strip(self, rank):
         return strip_from_bounds(self.bounds, rank, self.width, self.halo, self.align)
 
     def due(self):
-        """Balance on each of the first 8 frames, then every 8th."""
-        return self.world > 1 and (self.frames < 8 or self.frames % 8 == 0)
+        """Balance on each of the first 12 frames (except right after a move), then every 8th."""
+        return self.world > 1 and self.cooldown == 0 and (self.frames < 12 or self.frames % 8 == 0)
 
     def tick(self):
         self.frames += 1
+        if self.cooldown:
+            self.cooldown -= 1
 
     @staticmethod
     def _slowest(col_cost, bounds):
@@ -155,6 +159,7 @@ class StripBalancer:
         if new != self.bounds and self._slowest(col_cost, new) < (1.0 - self.gain) * self._slowest(col_cost, self.bounds):
             self.bounds = new
             self.changes += 1
+            self.cooldown = 2          # tick() of this frame takes one off: the NEXT frame is the one skipped
             return True
         return False
 
@@ -176,16 +181,25 @@ def assemble_on_root(mine, bounds, rank, world, dist, frame=None):
     import torch
     if world == 1:
         return mine
+    batched = dist.get_backend() == "nccl"      # one grouped NCCL launch instead of world-1 serialised p2p ops
     if rank != 0:
-        dist.send(mine, dst=0)
+        if batched:
+            for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0)]):
+                req.wait()
+        else:
+            dist.send(mine, dst=0)
         return None
     h, c = mine.shape[0], mine.shape[2]
     if frame is None:
         frame = torch.empty((h, bounds[-1], c), dtype=mine.dtype, device=mine.device)
     parts = [torch.empty((h, bounds[r + 1] - bounds[r], c), dtype=mine.dtype, device=mine.device) for r in range(1, world)]
-    reqs = [dist.irecv(p, src=r) for r, p in zip(range(1, world), parts)]
+    if batched:
+        reqs = dist.batch_isend_irecv([dist.P2POp(dist.irecv, p, r) for r, p in zip(range(1, world), parts)])
+    else:
+        reqs = [dist.irecv(p, src=r) for r, p in zip(range(1, world), parts)]
     frame[:, bounds[0]:bounds[1]] = mine
-    for r, (req, p) in enumerate(zip(reqs, parts), start=1):
+    for req in reqs:
         req.wait()
+    for r, p in enumerate(parts, start=1):
         frame[:, bounds[r]:bounds[r + 1]] = p
     return frame
