@@ -174,7 +174,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     W, H, K, Wu = args.width, args.height, args.steps, max(3, args.warmup)
     if world > 1:
-        Wu = max(Wu, 10)                                  # the strip edges settle during warm-up (tiles.StripBalancer); reported as `warmup`
+        Wu = max(Wu, 20)                                  # the strip edges settle during warm-up (tiles.StripBalancer); reported as `warmup`
     stream = torch.cuda.Stream()
     tb = Testbed(local_rank, stream=stream)
     model = common.model("fox16x2")
@@ -295,7 +295,8 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 march / f16 MLP (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "resolution": [W, H], "scene": args.scene, "parallelism": (f"{world} column strips, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves)" if world > 1 else "single GPU"),
                        "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples / K, "rays_marched_per_frame": rays / K, "march_stats_last_frame": march_stats,
-                       "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()}},
+                       "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()},
+                       "step_ms_min_med_max": [round(float(np.min(step_ms)), 4), round(float(np.median(step_ms)), 4), round(float(np.max(step_ms)), 4)]},
             "e2e": {"value": n_rays_total * K / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / K * 1e3},
             "gpu_launches": launches,
             "clocks": clocks,

@@ -181,6 +181,16 @@ class Engine:
         self._rgba_store = torch.empty(res_width * res_height * 4, dtype=torch.float32, device=tb.device)
         self._depth_store = torch.empty(res_width * res_height, dtype=torch.float32, device=tb.device)
         self._bind_outputs(tile)
+        if tile is not None:
+            # size every grow-only scratch buffer of the context for the FULL frame once, so that moving the tile later
+            # (tiles.StripBalancer) never reallocates (cudaFree is a device-wide sync and would stall in-flight NCCL traffic)
+            keep, self.tile = self.tile, None
+            self._bind_outputs(None)
+            self.frame(sync=True)
+            self.frame_index -= 1
+            self.tile = keep
+            self._bind_outputs(keep)
+            tb._check(tb.lib.snb_seed_rng(tb.ctx, 1999), "snb_seed_rng")
 
     def _bind_outputs(self, tile):
         w, h = (tile.w, tile.h) if tile is not None else (self.width, self.height)

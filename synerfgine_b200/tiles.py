@@ -142,8 +142,8 @@ class StripBalancer:
         return strip_from_bounds(self.bounds, rank, self.width, self.halo, self.align)
 
     def due(self):
-        """Balance on each of the first 12 frames (except right after a move), then every 8th."""
-        return self.world > 1 and self.cooldown == 0 and (self.frames < 12 or self.frames % 8 == 0)
+        """Balance on each of the first 16 frames (except right after a move), then every 8th."""
+        return self.world > 1 and self.cooldown == 0 and (self.frames < 16 or self.frames % 8 == 0)
 
     def tick(self):
         self.frames += 1
