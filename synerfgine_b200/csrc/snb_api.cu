@@ -86,7 +86,7 @@ void snb_destroy(snb_ctx* c) {
 	if (!c) return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
-	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_coarse, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
+	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
 	                  &c->d_counters, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
@@ -144,6 +144,13 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	d.rgb_act = m->rgb_activation; d.density_act = m->density_activation;
 	d.min_transmittance = m->min_transmittance;
 	d.env.bitfield = m->bitfield ? c->d_bitfield.as<uint8_t>() : nullptr;
+	d.env.bits_xyz = nullptr;
+	if (m->bitfield) {
+		SNB_CUDA(c, c->d_bits_xyz.reserve(bf_bytes));
+		k_bitfield_to_linear<<<((uint32_t)bf_bytes + 127) / 128, 128, 0, c->stream>>>(c->d_bitfield.as<uint8_t>(), (uint32_t)bf_bytes, c->d_bits_xyz.as<uint8_t>());
+		SNB_LAUNCHED(c);
+		d.env.bits_xyz = c->d_bits_xyz.as<uint8_t>();
+	}
 	d.env.min_mip = 0; d.env.max_mip = m->max_cascade;
 	d.env.render_aabb.lo = ld3(m->render_aabb_min); d.env.render_aabb.hi = ld3(m->render_aabb_max);
 	d.env.to_local = ldm3(m->render_aabb_to_local);

@@ -49,7 +49,7 @@ struct snb_ctx {
 	bool has_model = false;
 	snb::DevModel model;
 	uint32_t feat_per_level = 2;
-	snb::DevBuf d_grid, d_mlp, d_mlp_frag, d_mlp_umma, d_bitfield, d_coarse;
+	snb::DevBuf d_grid, d_mlp, d_mlp_frag, d_mlp_umma, d_bitfield, d_bits_xyz, d_coarse;
 
 	// scene
 	std::vector<snb::ObjectStore> obj_store;

@@ -14,6 +14,10 @@
 #pragma once
 #include "snb_math.cuh"
 
+#ifndef SNB_GATHER_HINT
+#define SNB_GATHER_HINT 0   // L1 eviction-priority hints on the gathers (tuning hook)
+#endif
+
 namespace snb {
 
 constexpr uint32_t kGridSize = 128;
@@ -49,7 +53,9 @@ constexpr int kCoarseRes = 32;
 constexpr int kCoarseWords = kCoarseRes * kCoarseRes * kCoarseRes / 32;   // 1024 words = 4 KB (staged in shared memory)
 
 struct MarchEnv {
-	const uint8_t* bitfield;   // kCascades * 128^3 / 8 bytes, Morton order per cascade; nullptr = all occupied
+	const uint8_t* bitfield;   // kCascades * 128^3 / 8 bytes, Morton order per cascade (the reference's layout); nullptr = all occupied
+	const uint8_t* bits_xyz;   // device-side copy of the same bits in x-fastest linear order per cascade (k_bitfield_to_linear):
+	                           // the DDA probes cells ~2.5 times per step and a Morton index costs ~28 instructions, a linear one 3
 	uint32_t min_mip, max_mip;
 	Aabb render_aabb;
 	m3 to_local;               // render_aabb_to_local
@@ -82,11 +88,31 @@ SNB_HD uint32_t cascade_cell(v3 pos, uint32_t mip) {
 	return morton3((uint32_t)ix, (uint32_t)iy, (uint32_t)iz);
 }
 
+#ifdef __CUDACC__
+// Same predicate as cell_occupied below, read from the linear-order copy. The cell coordinates are computed exactly as in
+// cascade_cell (cascaded_grid_idx_at); only the bit's address differs.
+SNB_D bool cell_occupied_xyz(v3 pos, const uint8_t* __restrict__ bits_xyz, uint32_t mip) {
+	const float mip_scale = pow2i(-(int)mip);
+	pos = pos - 0.5f;
+	pos = pos * mip_scale;
+	pos = pos + 0.5f;
+	const int ix = (int)(pos.x * (float)kGridSize), iy = (int)(pos.y * (float)kGridSize), iz = (int)(pos.z * (float)kGridSize);
+	if ((uint32_t)(ix | iy | iz) >= kGridSize) return false;      // any coordinate negative or >= 128
+	const uint32_t idx = (uint32_t)ix | ((uint32_t)iy << 7) | ((uint32_t)iz << 14) | (mip << 21);
+	return (__ldg(bits_xyz + (idx >> 3)) >> (idx & 7u)) & 1u;
+}
+#endif
+
 SNB_HD bool cell_occupied(v3 pos, const uint8_t* bitfield, uint32_t mip) {
 	const uint32_t idx = cascade_cell(pos, mip);
 	if (idx == 0xFFFFFFFFu) return false;
 #ifdef __CUDA_ARCH__
+#if SNB_GATHER_HINT
+	uint32_t byte;   // keep the bitfield in L1 against the hash-grid gathers streaming through it
+	asm("ld.global.nc.L1::evict_last.u8 %0, [%1];" : "=r"(byte) : "l"(bitfield + (idx / 8 + (kGridCells * mip) / 8)));
+#else
 	const uint8_t byte = __ldg(bitfield + (idx / 8 + (kGridCells * mip) / 8));
+#endif
 #else
 	const uint8_t byte = bitfield[idx / 8 + (kGridCells * mip) / 8];
 #endif
@@ -182,6 +208,14 @@ SNB_HD bool coarse_clear_ahead(v3 pos, v3 d, const MarchEnv& env) {
 	return false;
 }
 
+SNB_HD bool env_cell_occupied(v3 pos, const MarchEnv& env, uint32_t mip) {
+#ifdef __CUDA_ARCH__
+	return cell_occupied_xyz(pos, env.bits_xyz, mip);
+#else
+	return cell_occupied(pos, env.bitfield, mip);
+#endif
+}
+
 // Skip empty space: returns the first t >= t_in whose enclosing cascade cell is occupied, or kMaxDepth
 // once the ray leaves the render box. Every kLookAheadEvery-th empty cell the coarse grid is consulted: if nothing
 // can be occupied ahead, the remaining DDA steps (which could only end in kMaxDepth) are not walked.
@@ -192,9 +226,9 @@ SNB_HD float skip_to_occupied(float t, v3 o, v3 d, v3 idir, const MarchEnv& env)
 		const v3 pos = o + d * t;
 		if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) return kMaxDepth;
 		uint32_t mip = clamp_mip(mip_of(pos), env);
-		if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) return t;
+		if (!env.bitfield || env_cell_occupied(pos, env, mip)) return t;
 		if ((n_empty++ % kLookAheadEvery) == 0 && coarse_clear_ahead(pos, d, env)) return kMaxDepth;
-		while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
+		while (mip < env.max_mip && !env_cell_occupied(pos, env, mip + 1)) ++mip;
 		t = advance_past_voxel(t, env.st, pos, d, idir, mip);
 	}
 }

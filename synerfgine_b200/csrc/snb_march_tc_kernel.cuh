@@ -90,9 +90,9 @@ k_nerf_march_tc(DevModel model, DevView view, NerfOut out, int render_mode, cons
 				const v3 pos = o + d * t;
 				if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { finish(); break; }   // left the volume
 				uint32_t mip = clamp_mip(mip_of(pos), env);
-				if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) { searching = false; n_empty = 0; break; }
+				if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { searching = false; n_empty = 0; break; }
 				if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { finish(); break; }
-				while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
+				while (mip < env.max_mip && !cell_occupied_xyz(pos, env.bits_xyz, mip + 1)) ++mip;
 				t = advance_past_voxel(t, env.st, pos, d, idir, mip);
 				++n_dda;
 			}

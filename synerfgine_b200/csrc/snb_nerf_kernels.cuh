@@ -89,6 +89,22 @@ __global__ void __launch_bounds__(128) k_build_coarse(const uint8_t* __restrict_
 	}
 }
 
+// ---- linear-order copy of the occupancy bitfield (once per model) ---------------------------------------------------------
+// One thread per output byte = 8 x-consecutive cells of one cascade; bit (x, y, z) of cascade m comes from Morton bit
+// morton3(x, y, z) of the reference-layout bitfield. Read by cell_occupied_xyz (snb_march.cuh).
+__global__ void __launch_bounds__(128) k_bitfield_to_linear(const uint8_t* __restrict__ morton_bits, uint32_t n_bytes, uint8_t* __restrict__ bits_xyz) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_bytes) return;
+	const uint32_t mip = i / (kGridCells / 8), cell0 = (i % (kGridCells / 8)) * 8;
+	const uint32_t x0 = cell0 & 127u, y = (cell0 >> 7) & 127u, z = cell0 >> 14;
+	uint32_t out = 0;
+	for (uint32_t j = 0; j < 8; ++j) {
+		const uint32_t m = morton3(x0 + j, y, z);
+		out |= ((uint32_t)(morton_bits[mip * (kGridCells / 8) + (m >> 3)] >> (m & 7u)) & 1u) << j;
+	}
+	bits_xyz[i] = (uint8_t)out;
+}
+
 // ---- ray generation: one thread per tile pixel, 8x4 pixel patches per warp so queue neighbours are image neighbours ----
 __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail) {
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -238,10 +254,10 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { fin = true; searching = false; }   // left the volume
 					else {
 						uint32_t mip = clamp_mip(mip_of(pos), env);
-						if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) { valid = true; searching = false; n_empty = 0; }
+						if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { valid = true; searching = false; n_empty = 0; }
 						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { fin = true; searching = false; }
 						else {
-							while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
+							while (mip < env.max_mip && !cell_occupied_xyz(pos, env.bits_xyz, mip + 1)) ++mip;
 							t = advance_past_voxel_call(t, env.st, pos, d, idir, mip);
 						}
 					}

@@ -99,6 +99,15 @@ __device__ __noinline__ uint32_t grid_cell_index_slow(uint32_t hashmap_size, uin
 // (z*P2 | +P2)), which is the reference's index for each corner in uint32 arithmetic, evaluated once instead of 8 times.
 struct LevelFrac { float rx, ry, rz; };
 
+// Gathers of the hashed (fine) levels have next to no reuse beyond the x-neighbour that shares their 32 B sector: they are
+// allocated in L1 as first-to-evict, so that the occupancy bitfield and the dense coarse levels keep their lines.
+#if SNB_GATHER_HINT
+SNB_D unsigned short ldg_stream(const unsigned short* p) { unsigned short v; asm("ld.global.nc.L1::evict_first.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v; }
+SNB_D uint32_t ldg_stream(const uint32_t* p) { uint32_t v; asm("ld.global.nc.L1::evict_first.b32 %0, [%1];" : "=r"(v) : "l"(p)); return v; }
+SNB_D uint2 ldg_stream(const uint2* p) { uint2 v; asm("ld.global.nc.L1::evict_first.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p)); return v; }
+SNB_D uint4 ldg_stream(const uint4* p) { uint4 v; asm("ld.global.nc.L1::evict_first.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p)); return v; }
+#endif
+
 // Part 1: position in the level, corner indices (idx_out for the parity tap), issue the 8 gathers.
 template <int F, bool TAP>
 SNB_D void level_gather(const LevelDesc& L, v3 x, typename FeatVec<F>::T (&vals)[8], LevelFrac& fr, uint32_t* idx_out) {
@@ -126,8 +135,16 @@ SNB_D void level_gather(const LevelDesc& L, v3 x, typename FeatVec<F>::T (&vals)
 	}
 	typedef typename FeatVec<F>::T V;
 	const V* base = reinterpret_cast<const V*>(L.base);
+#if SNB_GATHER_HINT
+	if (L.mode == kLevelHashed) {
 #pragma unroll
-	for (int c = 0; c < 8; ++c) vals[c] = __ldg(base + idx[c]);
+		for (int c = 0; c < 8; ++c) vals[c] = ldg_stream(base + idx[c]);
+	} else
+#endif
+	{
+#pragma unroll
+		for (int c = 0; c < 8; ++c) vals[c] = __ldg(base + idx[c]);
+	}
 	if (TAP) {
 #pragma unroll
 		for (int c = 0; c < 8; ++c) idx_out[c] = idx[c];

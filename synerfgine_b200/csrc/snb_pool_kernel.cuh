@@ -157,9 +157,9 @@ k_nerf_march_pool(DevModel model, DevView view, NerfOut out, int render_mode, co
 					const v3 pos = o + d * t;
 					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { s = kSlotEmpty; break; }   // left the volume
 					uint32_t mip = clamp_mip(mip_of(pos), env);
-					if (!env.bitfield || cell_occupied(pos, env.bitfield, mip)) { s = kSlotReady; n_empty = 0; break; }
+					if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { s = kSlotReady; n_empty = 0; break; }
 					if (((n_empty++) & (uint32_t)(kLookAheadEvery - 1)) == 0u && coarse_clear_ahead(pos, d, env)) { s = kSlotEmpty; break; }
-					while (mip < env.max_mip && !cell_occupied(pos, env.bitfield, mip + 1)) ++mip;
+					while (mip < env.max_mip && !cell_occupied_xyz(pos, env.bits_xyz, mip + 1)) ++mip;
 					t = advance_past_voxel(t, env.st, pos, d, idir, mip);
 					++n_dda;
 				}
@@ -242,7 +242,7 @@ k_nerf_march_pool(DevModel model, DevView view, NerfOut out, int render_mode, co
 				uint32_t s = kSlotSearch;
 				if (t < kMaxDepth && env.render_aabb.contains(mul(env.to_local, npos))) {
 					const uint32_t mip = clamp_mip(mip_of(npos), env);
-					if (!env.bitfield || cell_occupied(npos, env.bitfield, mip)) s = kSlotReady;
+					if (!env.bitfield || cell_occupied_xyz(npos, env.bits_xyz, mip)) s = kSlotReady;
 				}
 				P.t[jr][lane] = t;
 				P.meta[jr][lane] = meta_pack(s, k, 0u, step_i);
