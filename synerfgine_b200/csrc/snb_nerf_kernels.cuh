@@ -172,7 +172,10 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 #ifndef SNB_LANE_CTAS
 #define SNB_LANE_CTAS 4     // resident CTAs per SM the register budget is set for (tuning hook)
 #endif
-constexpr int kMinFill = 26;
+#ifndef SNB_LANE_MIN_FILL
+#define SNB_LANE_MIN_FILL 20   // lanes holding a sample before the network runs (tuning hook)
+#endif
+constexpr int kMinFill = SNB_LANE_MIN_FILL;
 template <int F, bool ALT>
 __global__ void __launch_bounds__(kFusedThreads, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,

@@ -15,6 +15,10 @@
 #pragma once
 #include "snb_device.cuh"
 
+#ifndef SNB_ENC_GROUP
+#define SNB_ENC_GROUP 2   // hash-grid levels gathered together per loop trip (ILP vs code size; tuning hook)
+#endif
+
 namespace snb {
 
 // ---- weight fragment order for mma.m16n8k16 (B operand = W[n][k], "col" layout) --------------------------------
@@ -198,7 +202,7 @@ SNB_D void level_blend(const typename FeatVec<F>::T (&vals)[8], const LevelFrac&
 template <int F, bool TAP, int CS = 16>
 SNB_D void encode_position_to_row(const LevelDesc* __restrict__ levels, v3 x, __half* row, uint32_t* idx_out) {
 	constexpr int L = kFeat / F;
-	constexpr int G = F <= 2 ? 2 : 1;
+	constexpr int G = F <= 2 ? SNB_ENC_GROUP : 1;
 	typedef typename FeatVec<F>::T V;
 #pragma unroll 1
 	for (int l0 = 0; l0 < L; l0 += G) {
