@@ -116,8 +116,12 @@ void snb_destroy(snb_ctx* ctx);
 const char* snb_last_error(const snb_ctx* ctx);
 int snb_sync(snb_ctx* ctx);
 const char* snb_version(void);
-/* Implementation selectors (A/B measurements; results are identical within the parity contract): "march" = "pool" | "lane",
- * "mlp" = "mma" (warp-level mma.sync) | "tc" (CTA-level tcgen05 + TMEM). Environment SNB_MARCH / SNB_MLP set the defaults. */
+/* Implementation selectors (A/B measurements; results are identical within the parity contract):
+ *   "march"      = "lane" (default: ray per lane, warp-level mma.sync) | "pool" (warp-autonomous ray pool) | "tc" (CTA tiles, tcgen05 + TMEM)
+ *   "mlp"        = "mma" | "tc"   evaluator of the snb_network_inference parity tap
+ *   "overlap"    = "1" | "0"      mesh layer on a second stream
+ *   "dead_terms" = "1" | "0"      skip NeRF shadow terms that no written pixel can observe (identical frame and RNG states)
+ * Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS set the defaults. */
 int snb_set_option(snb_ctx* ctx, const char* key, const char* value);
 
 /* ---- inputs ------------------------------------------------------------------------------------------- */

@@ -51,6 +51,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		else return c->fail(SNB_ERR_ARG, "mlp: expected mma | tc");
 	} else if (k == "overlap") {
 		c->overlap_layers = v != "0";
+	} else if (k == "dead_terms") {
+		c->skip_dead_terms = v != "0";
 	} else return c->fail(SNB_ERR_ARG, "unknown option");
 	return SNB_OK;
 }
@@ -73,6 +75,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	if (const char* mv = getenv("SNB_MARCH")) snb_set_option(c, "march", mv);
 	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
 	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
+	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
 	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }

@@ -82,6 +82,7 @@ struct snb_ctx {
 	cudaStream_t stream2 = nullptr;
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_layers = true;
+	bool skip_dead_terms = true;   // k_nerf_shadow_terms: skip terms no written pixel can observe (option "dead_terms")
 
 	int fail(int code, const std::string& msg) { err = msg; return code; }
 	int cuda_fail(cudaError_t e, const char* what) {

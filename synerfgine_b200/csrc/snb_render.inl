@@ -150,7 +150,9 @@ static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int
 		SNB_CUDA(c, c->d_terms.reserve((size_t)n * 4));
 		MarchEnv env = c->model.env; env.min_mip = 0;
 		k_nerf_shadow_terms<<<(n + 127) / 128, 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
-		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>());
+		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(),
+		                                                            (render_mode != 8 && c->skip_dead_terms) ? reinterpret_cast<const float4*>(fb) : nullptr, dv.tw, dv.th,
+		                                                            rt->nerf_shadow_kernel / 2);
 		SNB_LAUNCHED(c);
 		k_nerf_shadow_apply<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, rt->nerf_shadow_kernel / 2, rt->nerf_shadow_intensity, render_mode, c->d_terms.as<float>(),
 		                                                  reinterpret_cast<float4*>(fb), nullptr);

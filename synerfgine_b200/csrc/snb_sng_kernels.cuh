@@ -321,11 +321,35 @@ __global__ void __launch_bounds__(128) k_raytrace(uint32_t n, const float* __res
 }
 
 // Mesh shadows on the NeRF, pass 1: one shadow term per NeRF pixel from its world position / normal.
+//
+// Dead-term elimination (`layer` != nullptr): pass 2 multiplies srgb_to_linear(rgb(p)) by the window mean around p, and a pixel
+// the march never wrote has rgb == 0 (frame buffer cleared by ray generation), so its output is 0 whatever the mean is. term(q)
+// is therefore only ever observable through a pixel p of q's window that the march wrote (alpha(p) > 0). When no such pixel
+// exists the BVH traversal and the shadow DDA are skipped; the RNG still draws what light_sample would have drawn, so the
+// generator states — and with them every later frame — stay identical. Not used in ShadowDepth mode (which shows the mean itself).
 __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const float* __restrict__ positions, const float* __restrict__ normals, MarchEnv env, DevScene sc,
-                                                          float intensity, float thr, Rng* __restrict__ rng_states, float* __restrict__ terms) {
+                                                          float intensity, float thr, Rng* __restrict__ rng_states, float* __restrict__ terms,
+                                                          const float4* __restrict__ layer, int width, int height, int half_k) {
 	const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
 	if (q >= n) return;
 	Rng rng = rng_states[q];
+	bool observable = true;
+	if (layer) {
+		observable = layer[q].w > 0.0f;
+		if (!observable) {
+			const int x = (int)(q % (uint32_t)width), y = (int)(q / (uint32_t)width);
+			for (int j = max(0, y - half_k); j <= min(height - 1, y + half_k) && !observable; ++j)
+				for (int i = max(0, x - half_k); i <= min(width - 1, x + half_k); ++i)
+					if (layer[j * width + i].w > 0.0f) { observable = true; break; }
+		}
+	}
+	if (!observable) {
+		for (uint32_t i = 0; i < sc.n_lights; ++i)
+			if (sc.lights[i].type == 0) (void)light_sample(sc.lights[i], rng);
+		terms[q] = 1.0f;
+		rng_states[q] = rng;
+		return;
+	}
 	const v3 orig_pos = mk3(positions[q * 3], positions[q * 3 + 1], positions[q * 3 + 2]);
 	const v3 normal = mk3(normals[q * 3], normals[q * 3 + 1], normals[q * 3 + 2]);
 	float overall = 1.0f;

@@ -151,3 +151,29 @@ def test_engine_python_surface(snb):
     assert h_rgba.shape == (48, 64, 4) and np.isfinite(h_rgba).mean() > 0.8
     assert tb.launch_count() > 0
     tb.close()
+
+
+def test_dead_shadow_terms_skip_is_result_identical(snb):
+    """k_nerf_shadow_terms skips terms no written pixel can observe (option "dead_terms"): three consecutive frames — the
+    later ones depend on the RNG states the earlier ones left behind — must be bit-identical with the skip on and off."""
+    from synerfgine_b200 import Engine, Testbed
+
+    def run(flag):
+        tb = Testbed(0)
+        assert tb.lib.snb_set_option(tb.ctx, b"dead_terms", flag) == 0
+        tb.set_model(common.model("small16x2"))
+        eng = Engine()
+        eng.set_virtual_world_json(scenes.scene_json("c2"), scenes.mesh_dir())
+        eng.init(96, 64, tb)
+        frames = []
+        for _ in range(3):
+            a, d = eng.frame()
+            frames.append((a.cpu().numpy().copy(), d.cpu().numpy().copy()))
+        tb.close()
+        return frames
+
+    on, off = run(b"1"), run(b"0")
+    for (a, da), (b, db) in zip(on, off):
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+        np.testing.assert_array_equal(da.view(np.uint32), db.view(np.uint32))
+    assert (on[0][0][..., 3] > 0).mean() > 0.05 and (on[0][0][..., 3] == 0).mean() > 0.05   # the frame has both kinds of pixels
