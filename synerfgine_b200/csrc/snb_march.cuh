@@ -219,7 +219,10 @@ SNB_HD bool env_cell_occupied(v3 pos, const MarchEnv& env, uint32_t mip) {
 // Skip empty space: returns the first t >= t_in whose enclosing cascade cell is occupied, or kMaxDepth
 // once the ray leaves the render box. Every kLookAheadEvery-th empty cell the coarse grid is consulted: if nothing
 // can be occupied ahead, the remaining DDA steps (which could only end in kMaxDepth) are not walked.
-constexpr int kLookAheadEvery = 8;
+#ifndef SNB_LOOKAHEAD_EVERY
+#define SNB_LOOKAHEAD_EVERY 8   // empty cells between two look-ahead walks (power of two; tuning hook)
+#endif
+constexpr int kLookAheadEvery = SNB_LOOKAHEAD_EVERY;
 SNB_HD float skip_to_occupied(float t, v3 o, v3 d, v3 idir, const MarchEnv& env) {
 	int n_empty = 0;
 	while (true) {
