@@ -302,6 +302,7 @@ def run_ours(args, rank, local_rank, world):
             "clocks": clocks,
             "roofline": {"kernel": "k_nerf_march_fused", "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
                          "peak_source": f"{src} (MEASURED_PEAKS.json hbm_gbs)", "launch_ms": mm,
+                         "launch_ms_note": "CUDA events around the march launch on the context stream; the mesh layer runs concurrently on the second stream (SNB_OVERLAP=0: 4.13 ms alone)",
                          "note": "algorithmic bytes = samples x 512 B hash gather + rays x 64 B; the 24 MB table is L2-resident by design, so DRAM traffic << algorithmic bytes",
                          "tensor": {"achieved_tflops": samples / K * FLOP_PER_SAMPLE / (mm * 1e-3) / 1e12, "peak_tflops": tflops}},
         }
