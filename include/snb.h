@@ -110,6 +110,21 @@ typedef struct {
 	int32_t tonemap_curve;
 } snb_rt_params;
 
+/* ---- present stage ---------------------------------------------------------------------
+ * Replaces the GL blit of Display::present / transfer_texture (src/synerfgine/display.cu:153-264,266-303) with the FXAA
+ * fragment shader scripts/virtual_desc/main.frag:51-117, and Display::save_image's glReadPixels + stbi_write_png
+ * (display.cu:305-322): final float RGBA frame (row 0 = top) -> RGB8 window image (row 0 = top), headless.
+ * Foveation warp parameters are main.frag's FoveationWarp uniforms (display.cu:199-218); NULL = identity. */
+typedef struct snb_fov_warp {
+	float al, bl, cl, am, bm, ar, br, cr, switch_left, switch_right, inv_switch_left, inv_switch_right;
+} snb_fov_warp;
+int snb_present(snb_ctx* ctx, const float* rgba_dev, int in_w, int in_h, int out_w, int out_h, const float* clear_rgb /* 3 floats or NULL */,
+                const snb_fov_warp* warp_x, const snb_fov_warp* warp_y, uint8_t* rgb8_dev /* out_w*out_h*3 */);
+int snb_present_host(snb_ctx* ctx, const float* rgba_dev, int in_w, int in_h, int out_w, int out_h, const float* clear_rgb,
+                     const snb_fov_warp* warp_x, const snb_fov_warp* warp_y, uint8_t* rgb8_host);
+/* 8-bit RGB PNG of a host image (rows top-down), as Display::save_image writes `output-%03d.png` (display.cu:318-319). Pure host code. */
+int snb_write_png(const char* path, const uint8_t* rgb8_host, int width, int height);
+
 /* ---- lifetime ----------------------------------------------------------------------------------------- */
 int snb_create(int device, void* cuda_stream /* cudaStream_t or NULL */, snb_ctx** out);
 void snb_destroy(snb_ctx* ctx);

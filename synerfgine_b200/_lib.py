@@ -30,6 +30,10 @@ class Tile(C.Structure):
     _fields_ = [("x0", i32), ("y0", i32), ("w", i32), ("h", i32)]
 
 
+class FovWarp(C.Structure):
+    _fields_ = [(n, f32) for n in ("al", "bl", "cl", "am", "bm", "ar", "br", "cr", "switch_left", "switch_right", "inv_switch_left", "inv_switch_right")]
+
+
 class Object(C.Structure):
     _fields_ = [("nodes", pf32), ("tris", pf32), ("n_nodes", i32), ("n_tris", i32), ("rot", f32 * 9), ("pos", f32 * 3),
                 ("scale", f32), ("mat_id", i32)]
@@ -94,6 +98,9 @@ SIGNATURES = {
     "snb_bvh_build": (C.c_int, [pf32, i32, i32, pf32, i32, C.POINTER(i32)]),
     "snb_obj_load": (C.c_int, [C.c_char_p, pf32, i32, C.POINTER(i32)]),
     "snb_density_to_bitfield": (C.c_int, [vp, pf32, u32, C.POINTER(u8)]),
+    "snb_present": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, pf32, C.POINTER(FovWarp), C.POINTER(FovWarp), vp]),
+    "snb_present_host": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, pf32, C.POINTER(FovWarp), C.POINTER(FovWarp), vp]),
+    "snb_write_png": (C.c_int, [C.c_char_p, vp, C.c_int, C.c_int]),
 }
 
 _lib = None

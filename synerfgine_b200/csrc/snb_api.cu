@@ -8,6 +8,8 @@
 #include <cstdlib>
 #include <cmath>
 #include <algorithm>
+#include <cstdio>
+#include <vector>
 #include "snb_context.cuh"
 
 using namespace snb;
@@ -89,7 +91,7 @@ void snb_destroy(snb_ctx* c) {
 	if (!c) return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
-	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
+	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_present, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
 	                  &c->d_counters, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
@@ -254,3 +256,4 @@ int snb_reset_accumulation(snb_ctx* c) {
 
 #include "snb_render.inl"
 #include "snb_taps.inl"
+#include "snb_present.inl"

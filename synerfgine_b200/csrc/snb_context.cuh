@@ -14,6 +14,7 @@
 #include "snb_pool_kernel.cuh"
 #include "snb_mlp_tc.cuh"
 #include "snb_march_tc_kernel.cuh"
+#include "snb_present.cuh"
 #include "snb_sng_kernels.cuh"
 
 namespace snb {
@@ -49,7 +50,7 @@ struct snb_ctx {
 	bool has_model = false;
 	snb::DevModel model;
 	uint32_t feat_per_level = 2;
-	snb::DevBuf d_grid, d_mlp, d_mlp_frag, d_mlp_umma, d_bitfield, d_bits_xyz, d_coarse;
+	snb::DevBuf d_grid, d_mlp, d_mlp_frag, d_mlp_umma, d_bitfield, d_bits_xyz, d_coarse, d_present;
 
 	// scene
 	std::vector<snb::ObjectStore> obj_store;

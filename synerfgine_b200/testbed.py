@@ -197,6 +197,28 @@ class Engine:
         self.out_rgba = self._rgba_store[:h * w * 4].view(h, w, 4)
         self.out_depth = self._depth_store[:h * w].view(h, w)
 
+    def present(self, window_width=None, window_height=None, clear_color=(0.0, 0.0, 0.0), host=True):
+        """≙ Display::present minus the window (display.cu:266-303): FXAA blit of the last frame into an RGB8 window image,
+        rows top-down. Returns a uint8 numpy array [H, W, 3] (host=True) or a torch uint8 tensor on the device."""
+        tb = self.testbed
+        h, w = self.out_rgba.shape[0], self.out_rgba.shape[1]
+        ow, oh = window_width or w, window_height or h
+        cl = (C.c_float * 3)(*clear_color)
+        if host:
+            out = np.empty((oh, ow, 3), dtype=np.uint8)
+            tb._check(tb.lib.snb_present_host(tb.ctx, self.out_rgba.data_ptr(), w, h, ow, oh, cl, None, None, out.ctypes.data), "snb_present_host")
+            return out
+        out = torch.empty((oh, ow, 3), dtype=torch.uint8, device=tb.device)
+        tb._check(tb.lib.snb_present(tb.ctx, self.out_rgba.data_ptr(), w, h, ow, oh, cl, None, None, out.data_ptr()), "snb_present")
+        return out
+
+    def save_image(self, path, window_width=None, window_height=None):
+        """≙ Display::save_image (display.cu:305-322): the presented window as an 8-bit RGB PNG."""
+        img = self.present(window_width, window_height, host=True)
+        tb = self.testbed
+        tb._check(tb.lib.snb_write_png(str(path).encode(), img.ctypes.data, img.shape[1], img.shape[0]), "snb_write_png")
+        return img
+
     def set_syn_samples(self, n):
         self.rt.shadow_iters = n
 

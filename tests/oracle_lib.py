@@ -53,6 +53,7 @@ def load():
         "orc_syn_raytrace": (None, [u32, pf, pf, V, M, C.POINTER(Object), u32, C.POINTER(Material), u32, C.POINTER(Light), u32, C.POINTER(RtParams), pu32, pf, pf]),
         "orc_shade_nerf_shadows": (None, [C.c_int, C.c_int, M, pf, pf, C.POINTER(Object), u32, C.POINTER(Light), u32, C.POINTER(RtParams), pu32, C.c_int, pf, pf]),
         "orc_overlay": (None, [C.c_int, C.c_int, C.c_int, pf, pf, pf, pf, C.c_int, C.c_int, C.c_int, f32, f32, pf, pf]),
+        "orc_present": (None, [pf, C.c_int, C.c_int, C.c_int, C.c_int, pf, pf, pf, C.POINTER(C.c_uint8)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -105,4 +106,17 @@ def frame(model_desc, view, scene, rt, rng_seed=1999, n_frames=1):
         out.update(syn_rgba=acc_rgba.copy().reshape(h, w, 4), syn_depth=acc_depth.copy().reshape(h, w), nerf_rgba=fb.reshape(h, w, 4), nerf_depth=depth.reshape(h, w),
                    positions=pos.reshape(h, w, 3), normals=normals.reshape(h, w, 3), shadow=shadow.reshape(h, w), final=final.reshape(h, w, 4),
                    final_depth=final_depth.reshape(h, w))
+    return out
+
+
+def present(rgba, out_w, out_h, clear=(0.0, 0.0, 0.0), warp_x=None, warp_y=None):
+    """Oracle present stage (FXAA blit + blend + RGB8): rgba [h, w, 4] float32 -> uint8 [out_h, out_w, 3], rows top-down."""
+    lib = load()
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    out = np.zeros((out_h, out_w, 3), np.uint8)
+    cl = np.asarray(clear, np.float32)
+    wx = np.asarray(warp_x, np.float32) if warp_x is not None else None
+    wy = np.asarray(warp_y, np.float32) if warp_y is not None else None
+    lib.orc_present(P(rgba), rgba.shape[1], rgba.shape[0], out_w, out_h, P(cl), P(wx) if wx is not None else None, P(wy) if wy is not None else None,
+                    out.ctypes.data_as(C.POINTER(C.c_uint8)))
     return out

@@ -177,3 +177,56 @@ def test_dead_shadow_terms_skip_is_result_identical(snb):
         np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
         np.testing.assert_array_equal(da.view(np.uint32), db.view(np.uint32))
     assert (on[0][0][..., 3] > 0).mean() > 0.05 and (on[0][0][..., 3] == 0).mean() > 0.05   # the frame has both kinds of pixels
+
+
+# ---- present stage: bytes equal the oracle's -----------------------------------------------------------
+@pytest.mark.parametrize("in_wh,out_wh", [((96, 64), (96, 64)), ((96, 64), (192, 128)), ((97, 61), (64, 48)), ((8, 8), (3, 5))])
+def test_present_bytes_match_oracle(snb, in_wh, out_wh):
+    import torch
+    from synerfgine_b200 import Testbed
+    rng = np.random.default_rng(in_wh[0] * 7 + out_wh[1])
+    w, h = in_wh
+    img = rng.random((h, w, 4)).astype(np.float32)
+    img[: h // 2, : w // 2, 3] = 1.0                                    # opaque quadrant, translucent elsewhere
+    img[h // 3: h // 2, :, :3] = 0.0                                    # hard edges for FXAA to work on
+    img[:, w // 3: w // 2, :3] *= 1.5                                   # values above 1: clamped by the 8-bit pack
+    tb = Testbed(0)
+    dev = torch.from_numpy(img).cuda()
+    out = np.empty((out_wh[1], out_wh[0], 3), np.uint8)
+    clear = (C.c_float * 3)(0.1, 0.2, 0.3)
+    rc = tb.lib.snb_present_host(tb.ctx, dev.data_ptr(), w, h, out_wh[0], out_wh[1], clear, None, None, out.ctypes.data)
+    assert rc == 0, tb.lib.snb_last_error(tb.ctx)
+    ref = O.present(img, out_wh[0], out_wh[1], clear=(0.1, 0.2, 0.3))
+    np.testing.assert_array_equal(out, ref)                             # byte-exact: same fp32 operations in the same order
+    # foveation warp (piecewise quadratic): non-identity parameters on both axes
+    from synerfgine_b200._lib import FovWarp
+    wx = FovWarp(0.5, 0.6, 0.0, 1.2, -0.05, -0.5, 1.6, -0.1, 0.25, 0.75, 0.18, 0.85)
+    wy = FovWarp(0.4, 0.7, 0.0, 1.1, -0.02, -0.4, 1.5, -0.1, 0.3, 0.7, 0.25, 0.8)
+    rc = tb.lib.snb_present_host(tb.ctx, dev.data_ptr(), w, h, out_wh[0], out_wh[1], clear, C.byref(wx), C.byref(wy), out.ctypes.data)
+    assert rc == 0
+    as_list = lambda s: [getattr(s, n) for n, _ in s._fields_]
+    ref = O.present(img, out_wh[0], out_wh[1], clear=(0.1, 0.2, 0.3), warp_x=as_list(wx), warp_y=as_list(wy))
+    np.testing.assert_array_equal(out, ref)
+    tb.close()
+
+
+def test_engine_frame_to_png(snb, tmp_path):
+    """Engine.frame -> present -> output-001.png: the file decodes to the presented window, which equals the oracle's
+    present stage applied to the same frame."""
+    from synerfgine_b200 import Engine, Testbed
+    from test_host_cpu import decode_png
+    tb = Testbed(0)
+    tb.set_model(common.model("small16x2"))
+    eng = Engine()
+    eng.set_virtual_world_json(scenes.scene_json("c2"), scenes.mesh_dir())
+    eng.init(96, 64, tb)
+    rgba, _ = eng.frame()
+    frame = rgba.cpu().numpy().copy()
+    path = tmp_path / "output-001.png"
+    img = eng.save_image(path)
+    np.testing.assert_array_equal(decode_png(str(path)), img)
+    np.testing.assert_array_equal(img, O.present(frame, 96, 64))
+    dev = eng.present(host=False)
+    np.testing.assert_array_equal(dev.cpu().numpy(), img)
+    assert img.std() > 5                                                # a real picture, not a constant
+    tb.close()

@@ -235,3 +235,79 @@ def test_object_animation_rotates_about_axis_and_light_ping_pongs():
 def test_param_count_matches_oracle_layout(orc, kind):
     m = common.model(kind)
     assert m.desc().n_params == orc.orc_n_params(m.n_levels, m.n_feat, m.log2_T, 16, C.c_float(m.per_level_scale))
+
+
+# ---- present stage: oracle properties + the PNG writer (host code, no GPU) ---------------------------
+def decode_png(path):
+    """Minimal PNG reader for the test (8-bit RGB, filter types 0-4)."""
+    import struct
+    import zlib
+    with open(path, "rb") as f:
+        data = f.read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(data):
+        n, typ = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        crc, = struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(typ + body) & 0xFFFFFFFF == crc, "chunk CRC"
+        if typ == b"IHDR":
+            w, h, depth, ctype, comp, flt, lace = struct.unpack(">IIBBBBB", body)
+            assert (depth, ctype, comp, flt, lace) == (8, 2, 0, 0, 0)
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    raw = zlib.decompress(idat)
+    assert len(raw) == h * (w * 3 + 1)
+    rows = np.frombuffer(raw, np.uint8).reshape(h, w * 3 + 1)
+    assert (rows[:, 0] == 0).all()
+    return rows[:, 1:].reshape(h, w, 3).copy()
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 5), (640, 360), (301, 233)])
+def test_write_png_round_trip(snb, tmp_path, w, h):
+    rng = np.random.default_rng(w * 1000 + h)
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    path = str(tmp_path / "output-001.png")
+    assert snb.snb_write_png(path.encode(), img.ctypes.data, w, h) == 0
+    np.testing.assert_array_equal(decode_png(path), img)
+    assert snb.snb_write_png(path.encode(), None, w, h) == -1
+    assert snb.snb_write_png(b"/nonexistent-dir/x.png", img.ctypes.data, w, h) == -4
+
+
+def test_oracle_present_properties():
+    rng = np.random.default_rng(11)
+    h, w = 24, 40
+    # (1) a constant image stays constant: every tap reads the same colour, blend with alpha 1 ignores the clear colour
+    flat = np.empty((h, w, 4), np.float32); flat[...] = (0.25, 0.5, 0.75, 1.0)
+    out = O.present(flat, w, h, clear=(1.0, 0.0, 0.0))
+    assert (out == np.array([64, 128, 191], np.uint8)).all()            # floor(c * 255 + 0.5)
+    # (2) alpha 0 everywhere -> premultiplied rgb 0 + clear colour
+    clear = np.zeros((h, w, 4), np.float32)
+    out = O.present(clear, w, h, clear=(0.2, 0.4, 0.6))
+    assert (out == np.array([51, 102, 153], np.uint8)).all()
+    # (3) a smooth gradient has no edges: FXAA's blend stays within one 8-bit step of the plain bilinear blit, rows are top-down
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    grad = np.stack([xx / w, yy / h, 0.5 * np.ones_like(xx), np.ones_like(xx)], axis=2).astype(np.float32)
+    out = O.present(grad, w, h)
+    core = out[2:-2, 2:-2].astype(int)                                  # GL_REPEAT wraps at the border
+    expect = np.floor(grad[2:-2, 2:-2, :3] * 255 + 0.5).astype(int)
+    assert np.abs(core - expect).max() <= 1
+    assert out[2, 5, 1] < out[h - 3, 5, 1]                              # green grows downwards: row 0 is the top
+    # (4) a straight axis-aligned edge is left alone (FXAA samples ALONG the edge), a diagonal staircase is softened, and only there
+    edge = np.zeros((h, w, 4), np.float32); edge[..., 3] = 1.0; edge[:, w // 2:, :3] = 1.0
+    out = O.present(edge, w, h)
+    assert set(np.unique(out[3:-3, 3:-3])) == {0, 255}
+    stair = np.zeros((h, w, 4), np.float32); stair[..., 3] = 1.0; stair[(xx + yy) > (w + h) / 2, :3] = 1.0
+    out = O.present(stair, w, h)[3:-3, 3:-3, 0].astype(int)
+    dist = np.abs((xx + yy) - (w + h) / 2)[3:-3, 3:-3]
+    soft = (out > 0) & (out < 255)
+    assert soft.any() and dist[soft].max() <= 3.0
+    assert (out[dist > 4][(xx + yy)[3:-3, 3:-3][dist > 4] < (w + h) / 2] == 0).all()
+    # (5) window larger than the frame: bilinear upscale keeps the range and the orientation
+    img = rng.random((h, w, 4)).astype(np.float32); img[..., 3] = 1.0
+    up = O.present(img, 2 * w, 2 * h)
+    assert up.shape == (2 * h, 2 * w, 3) and up.min() >= 0
+    # (6) identity warp passed explicitly == default
+    ident = [0, 0, 0, 1, 0, 0, 0, 0, 0, 1, 0, 1]
+    np.testing.assert_array_equal(O.present(img, w, h, warp_x=ident, warp_y=ident), O.present(img, w, h))
