@@ -279,8 +279,29 @@ def run_ours(args, rank, local_rank, world):
             dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
         e2e_s = float(e2e_s.item())
 
+        # ---- present stage, timed on its own: FXAA blit of the final frame into an RGB8 window image ----
+        present = None
+        if world == 1:
+            out8 = torch.empty((H, W, 3), dtype=torch.uint8, device="cuda")
+            final_rgba = eng.frame(sync=True)[0]
+            ms = []
+            for i in range(3 + 10):
+                flush.zero_()
+                p0 = torch.cuda.Event(enable_timing=True); p1 = torch.cuda.Event(enable_timing=True)
+                p0.record(stream)
+                rc = lib.snb_present(ctx, final_rgba.data_ptr(), W, H, W, H, None, None, None, out8.data_ptr())
+                p1.record(stream); p1.synchronize()
+                assert rc == 0, lib.snb_last_error(ctx)
+                if i >= 3:
+                    ms.append(p0.elapsed_time(p1))
+            pm = float(np.mean(ms))
+            present = {"kernel": "k_present", "ms": round(pm, 4), "bound": "hbm", "algorithmic_bytes": W * H * 19,
+                       "achieved_gbs": round(W * H * 19 / (pm * 1e-3) / 1e9, 1), "note": "16 B in + 3 B out per pixel, L2 flushed before each launch"}
+
     if rank == 0:
         hbm, tflops, src = measured_peaks()
+        if present:
+            present["frac"] = round(present["achieved_gbs"] / hbm, 4)
         mm = float(np.mean(march_ms))
         algo_bytes = (samples * BYTES_PER_SAMPLE + rays * BYTES_PER_RAY) / K
         ach = algo_bytes / (mm * 1e-3) / 1e9
@@ -296,7 +317,8 @@ def run_ours(args, rank, local_rank, world):
             "config": {"workload": WORKLOAD, "resolution": [W, H], "scene": args.scene, "parallelism": (f"{world} column strips, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves)" if world > 1 else "single GPU"),
                        "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples / K, "rays_marched_per_frame": rays / K, "march_stats_last_frame": march_stats,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()},
-                       "step_ms_min_med_max": [round(float(np.min(step_ms)), 4), round(float(np.median(step_ms)), 4), round(float(np.max(step_ms)), 4)]},
+                       "step_ms_min_med_max": [round(float(np.min(step_ms)), 4), round(float(np.median(step_ms)), 4), round(float(np.max(step_ms)), 4)],
+                       "present_stage": present},
             "e2e": {"value": n_rays_total * K / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / K * 1e3},
             "gpu_launches": launches,
             "clocks": clocks,

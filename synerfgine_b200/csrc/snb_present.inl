@@ -14,7 +14,7 @@ int snb_present(snb_ctx* c, const float* rgba_dev, int in_w, int in_h, int out_w
 	if (!c || !rgba_dev || !rgb8_dev || in_w <= 0 || in_h <= 0 || out_w <= 0 || out_h <= 0) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));
 	const float3 clear = clear_rgb ? make_float3(clear_rgb[0], clear_rgb[1], clear_rgb[2]) : make_float3(0, 0, 0);
-	const dim3 grid2((out_w + 15) / 16, (out_h + 7) / 8);
+	const dim3 grid2((out_w + 31) / 32, (out_h + 3) / 4);
 	k_present<<<grid2, 128, 0, c->stream>>>(reinterpret_cast<const float4*>(rgba_dev), in_w, in_h, out_w, out_h, clear, load_warp(warp_x), load_warp(warp_y), rgb8_dev);
 	SNB_LAUNCHED(c);
 	return SNB_OK;
