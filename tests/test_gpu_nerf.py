@@ -161,3 +161,82 @@ def test_errors_are_reported_not_thrown(snb, ctx):
     bad = common.model("small16x2").desc(); bad.n_levels = 5
     assert snb.snb_set_model(ctx, C.byref(bad)) != 0
     assert b"n_levels" in snb.snb_last_error(ctx)
+
+
+# ---- BASELINE.json's full size (C2 model, 1920x1080) through size-independent properties ---------------------------------
+def _render_full(snb, ctx, v, tile=None, march=b"lane"):
+    from synerfgine_b200._lib import Tile
+    assert snb.snb_set_option(ctx, b"march", march) == 0
+    w, h = (tile.w, tile.h) if tile is not None else (v.width, v.height)
+    fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    pos, nrm = dev((h, w, 3), torch.float32), dev((h, w, 3), torch.float32)
+    rt = common.default_rt(show_shadow_on_nerf=0)
+    rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), C.byref(tile) if tile is not None else None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(),
+                                          pos.data_ptr(), nrm.data_ptr())
+    assert rc == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0, snb.snb_last_error(ctx)
+    cnt = (C.c_uint64 * 4)()
+    assert snb.snb_get_counters(ctx, cnt) == 0
+    snb.snb_set_option(ctx, b"march", b"lane")
+    return fb, depth, pos, (int(cnt[0]), int(cnt[1]), int(cnt[2]))
+
+
+def test_full_size_properties(snb, ctx):
+    """1080p frame of the benchmark model: (1) two runs are bit-identical (the queue order is not, the result must be);
+    (2) the ray-pool march visits exactly the same samples as the lane march and writes the same bits; (3) the tcgen05 march
+    evaluates the same samples (identical counters) and agrees within the fp16 tolerance; (4) four column strips with the
+    multi-GPU halo reproduce the full frame bit for bit, and their sample counts add up to at least the full frame's."""
+    from synerfgine_b200._lib import Tile
+    from synerfgine_b200 import tiles
+    m = common.model("fox16x2")
+    set_model(snb, ctx, m)
+    W, H = 1920, 1080
+    v = common.make_view(W, H, spp=1, snap=0)
+    a_fb, a_depth, a_pos, a_cnt = _render_full(snb, ctx, v)
+    b_fb, b_depth, b_pos, b_cnt = _render_full(snb, ctx, v)
+    assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt
+    assert a_cnt[0] > 5_000_000 and (a_fb[..., 3] > 0.5).float().mean() > 0.05
+    p_fb, p_depth, p_pos, p_cnt = _render_full(snb, ctx, v, march=b"pool")
+    assert p_cnt == a_cnt
+    assert torch.equal(p_fb, a_fb) and torch.equal(p_depth, a_depth) and torch.equal(p_pos, a_pos)
+    t_fb, t_depth, t_pos, t_cnt = _render_full(snb, ctx, v, march=b"tc")
+    err = (t_fb - a_fb).abs()
+    assert float(err.max()) <= 1e-2 and common.psnr(t_fb.cpu().numpy(), a_fb.cpu().numpy()) >= 50.0
+    assert abs(t_cnt[0] - a_cnt[0]) <= 1e-3 * a_cnt[0] and t_cnt[1] == a_cnt[1]     # a ray may saturate one sample earlier or later
+    halo, total = tiles.halo_for(4), 0
+    for r in range(4):
+        s = tiles.strip_for(r, 4, W, halo)
+        fb, depth, pos, cnt = _render_full(snb, ctx, v, tile=Tile(s.hx0, 0, s.render_width, H))
+        assert torch.equal(fb[:, s.crop], a_fb[:, s.x0:s.x1]) and torch.equal(depth[:, s.crop], a_depth[:, s.x0:s.x1])
+        assert torch.equal(pos[:, s.crop], a_pos[:, s.x0:s.x1])
+        total += cnt[0]
+    assert a_cnt[0] <= total <= 1.05 * a_cnt[0]                                      # the halo columns are marched twice
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (3, 2), (33, 1), (1, 37)])
+def test_degenerate_frame_sizes(snb, orc, ctx, w, h):
+    """Ragged inputs: frames smaller than a warp's 8x4 patch, single rows and columns."""
+    m = common.model("small16x2")
+    d = set_model(snb, ctx, m)
+    v = common.make_view(w, h)
+    fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    rfb, rdepth, _, _ = O.render_nerf(d, v, 0)
+    assert np.abs(fb.cpu().numpy() - rfb).max() <= 1e-2
+
+
+def test_camera_that_sees_nothing(snb, ctx):
+    """Empty input: every ray misses the volume -> zero rays queued, zero samples, a cleared frame, no hang."""
+    m = common.model("small16x2")
+    set_model(snb, ctx, m)
+    v = common.make_view(64, 48)
+    for i in (6, 7, 8):
+        v.camera[i] = -v.camera[i]                                                     # forward column negated: the eye looks away from the box
+    fb, depth = dev((48, 64, 4), torch.float32), dev((48, 64), torch.float32)
+    fb.fill_(7.0)
+    assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    cnt = (C.c_uint64 * 4)()
+    assert snb.snb_get_counters(ctx, cnt) == 0
+    assert int(cnt[0]) == 0 and float(fb.abs().max()) == 0.0
