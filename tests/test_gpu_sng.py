@@ -230,3 +230,30 @@ def test_engine_frame_to_png(snb, tmp_path):
     np.testing.assert_array_equal(dev.cpu().numpy(), img)
     assert img.std() > 5                                                # a real picture, not a constant
     tb.close()
+
+
+def test_empty_world_is_the_nerf_layer_alone(snb, orc, ctx):
+    """Edge case: a virtual world with no objects and no lights (the reference's Engine runs like that before a scene file is
+    loaded): the mesh layer is empty, every shadow term is 1, and the frame still matches the oracle."""
+    import json
+    from synerfgine_b200.scene import Scene
+    m = common.model("small16x2")
+    d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
+    j = json.loads(scenes.scene_json("c2"))
+    j["objfile"], j["lights"] = [], []
+    sc = Scene(json.dumps(j), scenes.mesh_dir())
+    assert sc.n_objects == 0 and sc.n_lights == 0
+    rc = snb.snb_set_scene(ctx, sc.objects, 0, sc.materials, sc.n_materials, sc.lights, 0)
+    assert rc == 0, snb.snb_last_error(ctx)
+    rt = sc.rt.copy()
+    w, h = 64, 48
+    v = common.make_view(w, h)
+    assert snb.snb_seed_rng(ctx, 1999) == 0 and snb.snb_reset_accumulation(ctx) == 0
+    out, od = dev((h, w, 4)), dev((h, w))
+    rc = snb.snb_frame(ctx, C.byref(v), None, C.byref(rt), out.data_ptr(), od.data_ptr())
+    assert rc == 0, snb.snb_last_error(ctx)
+    assert snb.snb_sync(ctx) == 0
+    ref = O.frame(d, v, sc, rt, 1999, 1)
+    assert (ref["syn_depth"] >= 1000).all()
+    assert close_fraction(out.cpu().numpy(), ref["final"], 1e-2) > 0.99
+    assert finite_psnr(out.cpu().numpy(), ref["final"]) > 40
