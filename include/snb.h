@@ -136,7 +136,8 @@ const char* snb_version(void);
  *   "mlp"        = "mma" | "tc"   evaluator of the snb_network_inference parity tap
  *   "overlap"    = "1" | "0"      mesh layer on a second stream
  *   "dead_terms" = "1" | "0"      skip NeRF shadow terms that no written pixel can observe (identical frame and RNG states)
- * Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS set the defaults. */
+ *   "bands"      = "1" | "2"      2: generate the lower half's rays on a side stream while the upper half is marched (identical frame; measured slower)
+ * Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS / SNB_BANDS set the defaults. */
 int snb_set_option(snb_ctx* ctx, const char* key, const char* value);
 
 /* ---- inputs ------------------------------------------------------------------------------------------- */

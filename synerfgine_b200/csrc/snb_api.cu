@@ -53,6 +53,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		else return c->fail(SNB_ERR_ARG, "mlp: expected mma | tc");
 	} else if (k == "overlap") {
 		c->overlap_layers = v != "0";
+	} else if (k == "bands") {
+		c->bands = v == "2" ? 2 : 1;
 	} else if (k == "dead_terms") {
 		c->skip_dead_terms = v != "0";
 	} else return c->fail(SNB_ERR_ARG, "unknown option");
@@ -78,6 +80,9 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
 	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
 	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
+	if (const char* mv = getenv("SNB_BANDS")) snb_set_option(c, "bands", mv);
+	if (cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_band0, cudaEventDisableTiming) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&c->ev_band1, cudaEventDisableTiming) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
 	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
@@ -96,6 +101,7 @@ void snb_destroy(snb_ctx* c) {
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
 	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	if (c->stream3) { cudaStreamSynchronize(c->stream3); cudaStreamDestroy(c->stream3); cudaEventDestroy(c->ev_band0); cudaEventDestroy(c->ev_band1); }
 	if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;

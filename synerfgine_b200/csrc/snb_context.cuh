@@ -80,7 +80,9 @@ struct snb_ctx {
 
 	// second stream for the mesh layer of snb_frame: it does not depend on the NeRF layer until the overlay, and both are
 	// latency-bound, so they run concurrently (the reference serialises them with host syncs, engine.cu:386-406)
-	cudaStream_t stream2 = nullptr;
+	cudaStream_t stream2 = nullptr, stream3 = nullptr;   // mesh layer; lower band's ray generation
+	cudaEvent_t ev_band0 = nullptr, ev_band1 = nullptr;
+	int bands = 1;                                          // option "bands": 2 was measured slower (7.18 vs 6.97 ms), kept for A/B
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_layers = true;
 	bool skip_dead_terms = true;   // k_nerf_shadow_terms: skip terms no written pixel can observe (option "dead_terms")

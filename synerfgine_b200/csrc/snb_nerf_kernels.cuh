@@ -106,10 +106,13 @@ __global__ void __launch_bounds__(128) k_bitfield_to_linear(const uint8_t* __res
 }
 
 // ---- ray generation: one thread per tile pixel, 8x4 pixel patches per warp so queue neighbours are image neighbours ----
-__global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail) {
+// Patches [patch_begin, patch_end) of the tile (row-major patch order): one launch per band of the frame.
+__global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail,
+                                                     int patch_begin, int patch_end) {
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int patches_x = (view.tw + 7) / 8;
-	const int patch = blockIdx.x * 4 + warp;
+	const int patch = patch_begin + blockIdx.x * 4 + warp;
+	if (patch >= patch_end) return;                            // whole warp
 	const int px = (patch % patches_x) * 8 + (lane & 7), py = (patch / patches_x) * 4 + (lane >> 3);
 	bool alive = false;
 	RayRec rec;
