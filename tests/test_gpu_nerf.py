@@ -240,3 +240,17 @@ def test_camera_that_sees_nothing(snb, ctx):
     cnt = (C.c_uint64 * 4)()
     assert snb.snb_get_counters(ctx, cnt) == 0
     assert int(cnt[0]) == 0 and float(fb.abs().max()) == 0.0
+
+
+def test_two_band_ray_generation_is_result_identical(snb, ctx):
+    """Option "bands" = 2 (lower half's rays generated on a side stream while the upper half is marched): same bits."""
+    m = common.model("small16x2")
+    set_model(snb, ctx, m)
+    v = common.make_view(320, 288, spp=1, snap=0)
+    assert snb.snb_set_option(ctx, b"bands", b"1") == 0
+    a = _render_full(snb, ctx, v)
+    assert snb.snb_set_option(ctx, b"bands", b"2") == 0
+    b = _render_full(snb, ctx, v)
+    assert snb.snb_set_option(ctx, b"bands", b"1") == 0
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and a[3] == b[3]
+    assert a[3][0] > 10000
