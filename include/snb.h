@@ -125,6 +125,20 @@ int snb_present_host(snb_ctx* ctx, const float* rgba_dev, int in_w, int in_h, in
 /* 8-bit RGB PNG of a host image (rows top-down), as Display::save_image writes `output-%03d.png` (display.cu:318-319). Pure host code. */
 int snb_write_png(const char* path, const uint8_t* rgb8_host, int width, int height);
 
+/* ---- on-disk model format ------------------------------------------------------------------
+ * instant-ngp / SyNeRFgine snapshots: `.ingp` (zlib- or gzip-compressed msgpack) and `.msgpack`, as written by
+ * Testbed::save_snapshot and read by Testbed::load_snapshot (src/testbed.cu:4812-4992) with tcnn Trainer::serialize
+ * (tiny-cuda-nn/trainer.h:274-312). Pure host code. The model descriptor returned by snb_snapshot_get points INTO the
+ * snapshot object (params) and has bitfield == NULL: build it from the fp16 density grid with snb_density_to_bitfield
+ * (what load_snapshot does through update_density_grid_mean_and_bitfield, testbed.cu:4922-4931). */
+typedef struct snb_snapshot snb_snapshot;
+int snb_snapshot_load(const char* path, snb_snapshot** out, char* err, size_t err_len);
+void snb_snapshot_free(snb_snapshot* s);
+int snb_snapshot_get(const snb_snapshot* s, snb_model_desc* model, const uint16_t** density_fp16, uint64_t* n_density, uint32_t* aabb_scale,
+                     float* camera12 /* column-major mat4x3 or NULL */);
+int snb_snapshot_save(const char* path, const snb_model_desc* model, const uint16_t* density_fp16, uint64_t n_density, uint32_t aabb_scale,
+                      const float* camera12 /* or NULL */, int compress);
+
 /* ---- lifetime ----------------------------------------------------------------------------------------- */
 int snb_create(int device, void* cuda_stream /* cudaStream_t or NULL */, snb_ctx** out);
 void snb_destroy(snb_ctx* ctx);

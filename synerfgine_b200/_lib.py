@@ -101,6 +101,10 @@ SIGNATURES = {
     "snb_present": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, pf32, C.POINTER(FovWarp), C.POINTER(FovWarp), vp]),
     "snb_present_host": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, pf32, C.POINTER(FovWarp), C.POINTER(FovWarp), vp]),
     "snb_write_png": (C.c_int, [C.c_char_p, vp, C.c_int, C.c_int]),
+    "snb_snapshot_load": (C.c_int, [C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),
+    "snb_snapshot_free": (None, [vp]),
+    "snb_snapshot_get": (C.c_int, [vp, C.POINTER(ModelDesc), C.POINTER(C.POINTER(C.c_uint16)), C.POINTER(u64), C.POINTER(u32), pf32]),
+    "snb_snapshot_save": (C.c_int, [C.c_char_p, C.POINTER(ModelDesc), C.POINTER(C.c_uint16), u64, u32, pf32, C.c_int]),
 }
 
 _lib = None

@@ -72,7 +72,41 @@ class Testbed:
         self._check(self.lib.snb_set_model(self.ctx, C.byref(d)), "snb_set_model")
 
     def load_snapshot(self, path):
-        raise NotImplementedError(".ingp/.msgpack snapshot container is SURVEY §8(f) rank 2 (next rows); use set_model()")
+        """≙ Testbed::load_snapshot (src/testbed.cu:4878-4992): read the `.ingp` / `.msgpack` file, rebuild the occupancy
+        bitfield from the stored fp16 density grid on the GPU (update_density_grid_mean_and_bitfield), upload the model and
+        adopt the stored camera."""
+        h = C.c_void_p()
+        err = C.create_string_buffer(512)
+        rc = self.lib.snb_snapshot_load(str(path).encode(), C.byref(h), err, 512)
+        if rc != 0:
+            raise RuntimeError(f"load_snapshot({path}): {err.value.decode()} (status {rc})")
+        try:
+            d = _lib.ModelDesc(); dens = C.POINTER(C.c_uint16)(); n = C.c_uint64(); scale = C.c_uint32(); cam = (C.c_float * 12)()
+            rc = self.lib.snb_snapshot_get(h, C.byref(d), C.byref(dens), C.byref(n), C.byref(scale), cam)
+            has_camera = rc == 0
+            if rc not in (0, -3):
+                raise RuntimeError(f"snb_snapshot_get: status {rc}")
+            bits = None
+            if n.value:
+                density = np.ctypeslib.as_array(dens, shape=(n.value,)).view(np.float16).astype(np.float32)
+                bits = np.zeros(8 * 128 ** 3 // 8, dtype=np.uint8)
+                self._check(self.lib.snb_density_to_bitfield(self.ctx, _fp(density), d.max_cascade, bits.ctypes.data_as(C.POINTER(C.c_uint8))), "snb_density_to_bitfield")
+                d.bitfield = bits.ctypes.data_as(C.POINTER(C.c_uint8))
+            self._check(self.lib.snb_set_model(self.ctx, C.byref(d)), "snb_set_model")      # copies params and bitfield
+            self.model = None
+            self.aabb_scale = scale.value
+            if has_camera:
+                self.camera_matrix = np.array(list(cam), dtype=np.float32).reshape(4, 3)
+        finally:
+            self.lib.snb_snapshot_free(h)
+
+    def save_snapshot(self, path, model, compress=True):
+        """≙ Testbed::save_snapshot (src/testbed.cu:4812-4876) for a model object with .desc(), .density, .aabb_scale."""
+        d = model.desc()
+        dens = np.ascontiguousarray(model.density.astype(np.float16)).view(np.uint16)
+        cam = (C.c_float * 12)(*[float(x) for x in np.asarray(self.camera_matrix, dtype=np.float32).reshape(-1)])
+        self._check(self.lib.snb_snapshot_save(str(path).encode(), C.byref(d), dens.ctypes.data_as(C.POINTER(C.c_uint16)), dens.size, int(model.aabb_scale), cam, int(bool(compress))),
+                    "snb_snapshot_save")
 
     def set_camera_from_view(self, view, at, zoom):
         """≙ Engine::init applying the JSON camera block: set_view_dir, set_look_at, set_scale."""
