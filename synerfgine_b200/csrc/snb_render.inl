@@ -116,18 +116,22 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	return rc;
 }
 
+// Per-pixel generator states live in FULL-FRAME arrays indexed by the global pixel (the state belongs to the pixel, not to the
+// tile that happens to render it): seeded once per (seed, resolution) like Engine::resize does (engine.cu:236-255), and a tile
+// that moves between frames (tiles.StripBalancer) keeps using the same states without any re-seeding.
 static int ensure_rng(snb_ctx* c, const DevView& syn, const DevView& nerf) {
-	const bool same = !c->rng_dirty && c->rng_w == syn.width && c->rng_h == syn.height && c->rng_tx0 == syn.tx0 && c->rng_ty0 == syn.ty0 &&
-	                  c->rng_tw == syn.tw && c->rng_th == syn.th && c->rng_scale == syn.width / nerf.width;
-	if (same) return SNB_OK;
-	const uint32_t n_syn = (uint32_t)(syn.tw * syn.th), n_nerf = (uint32_t)(nerf.tw * nerf.th);
+	const bool same_tile = c->rng_tx0 == syn.tx0 && c->rng_ty0 == syn.ty0 && c->rng_tw == syn.tw && c->rng_th == syn.th;
+	const bool same_frame = !c->rng_dirty && c->rng_w == syn.width && c->rng_h == syn.height && c->rng_scale == syn.width / nerf.width;
+	if (!same_tile) { c->syn_reset = true; c->rng_tx0 = syn.tx0; c->rng_ty0 = syn.ty0; c->rng_tw = syn.tw; c->rng_th = syn.th; }   // the mesh layer's temporal blend is tile-local
+	if (same_frame) return SNB_OK;
+	const uint32_t n_syn = (uint32_t)(syn.width * syn.height), n_nerf = (uint32_t)(nerf.width * nerf.height);
 	SNB_CUDA(c, c->d_rng_syn.reserve((size_t)n_syn * sizeof(Rng)));
 	SNB_CUDA(c, c->d_rng_nerf.reserve((size_t)n_nerf * sizeof(Rng)));
-	k_init_rng<<<(n_syn + 127) / 128, 128, 0, c->stream>>>(n_syn, (unsigned long long)c->rng_seed, syn.width, syn.tx0, syn.ty0, syn.tw, c->d_rng_syn.as<Rng>());
+	k_init_rng<<<(n_syn + 127) / 128, 128, 0, c->stream>>>(n_syn, (unsigned long long)c->rng_seed, syn.width, 0, 0, syn.width, c->d_rng_syn.as<Rng>());
 	SNB_LAUNCHED(c);
-	k_init_rng<<<(n_nerf + 127) / 128, 128, 0, c->stream>>>(n_nerf, (unsigned long long)c->rng_seed, nerf.width, nerf.tx0, nerf.ty0, nerf.tw, c->d_rng_nerf.as<Rng>());
+	k_init_rng<<<(n_nerf + 127) / 128, 128, 0, c->stream>>>(n_nerf, (unsigned long long)c->rng_seed, nerf.width, 0, 0, nerf.width, c->d_rng_nerf.as<Rng>());
 	SNB_LAUNCHED(c);
-	c->rng_dirty = false; c->rng_w = syn.width; c->rng_h = syn.height; c->rng_tx0 = syn.tx0; c->rng_ty0 = syn.ty0; c->rng_tw = syn.tw; c->rng_th = syn.th;
+	c->rng_dirty = false; c->rng_w = syn.width; c->rng_h = syn.height;
 	c->rng_scale = syn.width / nerf.width;
 	c->syn_reset = true;
 	return SNB_OK;
@@ -160,7 +164,7 @@ static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* 
 		c->syn_reset = false;
 	}
 	k_raytrace<<<(n + 127) / 128, 128, 0, st>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
-	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>());
+	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>(), dv.width, dv.tx0, dv.ty0, dv.tw);
 	SNB_LAUNCHED(c);
 	c->stage_end(3, st);
 	return SNB_OK;
@@ -179,7 +183,7 @@ static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int
 		k_nerf_shadow_terms<<<(n + 127) / 128, 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
 		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(),
 		                                                            (render_mode != 8 && c->skip_dead_terms) ? reinterpret_cast<const float4*>(fb) : nullptr, dv.tw, dv.th,
-		                                                            rt->nerf_shadow_kernel / 2);
+		                                                            rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0);
 		SNB_LAUNCHED(c);
 		k_nerf_shadow_apply<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, rt->nerf_shadow_kernel / 2, rt->nerf_shadow_intensity, render_mode, c->d_terms.as<float>(),
 		                                                  reinterpret_cast<float4*>(fb), nullptr);

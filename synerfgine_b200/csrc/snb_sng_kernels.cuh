@@ -257,10 +257,12 @@ __global__ void __launch_bounds__(128) k_syn_raygen(DevView view, float* __restr
 
 // One thread per mesh-layer pixel: samples x bounces closest-hit + shading; 50/50 temporal blend into acc_rgba.
 __global__ void __launch_bounds__(128) k_raytrace(uint32_t n, const float* __restrict__ origins, const float* __restrict__ dirs, v3 up_vec, MarchEnv env,
-                                                  DevScene sc, RtParams rt, Rng* __restrict__ rng_states, float4* __restrict__ acc_rgba, float* __restrict__ acc_depth) {
+                                                  DevScene sc, RtParams rt, Rng* __restrict__ rng_states, float4* __restrict__ acc_rgba, float* __restrict__ acc_depth,
+                                                  int full_w, int tx0, int ty0, int tw) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
-	Rng rng = rng_states[i];
+	const size_t gi = (size_t)(ty0 + (int)(i / (uint32_t)tw)) * full_w + tx0 + (int)(i % (uint32_t)tw);   // generator states are per GLOBAL pixel
+	Rng rng = rng_states[gi];
 	const v3 src_position = mk3(origins[i * 3], origins[i * 3 + 1], origins[i * 3 + 2]);
 	const v3 src_direction = mk3(dirs[i * 3], dirs[i * 3 + 1], dirs[i * 3 + 2]);
 	v3 shade = mk3(0, 0, 0), normal = mk3(0, 0, 0), view_pos = mk3(0, 0, 0), next_pos = mk3(0, 0, 0), view_dir = mk3(0, 0, 0), next_dir = mk3(0, 0, 0);
@@ -317,7 +319,7 @@ __global__ void __launch_bounds__(128) k_raytrace(uint32_t n, const float* __res
 			outc = shade;
 	}
 	acc_rgba[i] = make_float4(outc.x, outc.y, outc.z, prev.w);
-	rng_states[i] = rng;
+	rng_states[gi] = rng;
 }
 
 // Mesh shadows on the NeRF, pass 1: one shadow term per NeRF pixel from its world position / normal.
@@ -329,10 +331,11 @@ __global__ void __launch_bounds__(128) k_raytrace(uint32_t n, const float* __res
 // generator states — and with them every later frame — stay identical. Not used in ShadowDepth mode (which shows the mean itself).
 __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const float* __restrict__ positions, const float* __restrict__ normals, MarchEnv env, DevScene sc,
                                                           float intensity, float thr, Rng* __restrict__ rng_states, float* __restrict__ terms,
-                                                          const float4* __restrict__ layer, int width, int height, int half_k) {
+                                                          const float4* __restrict__ layer, int width, int height, int half_k, int full_w, int tx0, int ty0) {
 	const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
 	if (q >= n) return;
-	Rng rng = rng_states[q];
+	const size_t gq = (size_t)(ty0 + (int)(q / (uint32_t)width)) * full_w + tx0 + (int)(q % (uint32_t)width);   // generator states are per GLOBAL pixel
+	Rng rng = rng_states[gq];
 	bool observable = true;
 	if (layer) {
 		observable = layer[q].w > 0.0f;
@@ -347,7 +350,7 @@ __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const flo
 		for (uint32_t i = 0; i < sc.n_lights; ++i)
 			if (sc.lights[i].type == 0) (void)light_sample(sc.lights[i], rng);
 		terms[q] = 1.0f;
-		rng_states[q] = rng;
+		rng_states[gq] = rng;
 		return;
 	}
 	const v3 orig_pos = mk3(positions[q * 3], positions[q * 3 + 1], positions[q * 3 + 2]);
@@ -372,7 +375,7 @@ __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const flo
 		}
 	}
 	terms[q] = overall;
-	rng_states[q] = rng;
+	rng_states[gq] = rng;
 }
 
 // Pass 2: (2*(K/2)+1)^2 window mean of the terms, pow, darken (with the reference's second srgb_to_linear).

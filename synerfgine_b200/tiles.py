@@ -126,9 +126,10 @@ def strip_from_bounds(bounds, rank, width, halo, align=1):
 
 class StripBalancer:
     """Per-frame feedback on the strip edges. `observe(col_cost)` takes the GLOBAL per-column cost (already all-reduced) and
-    moves the edges only when the predicted slowest strip gets at least `gain` (default 8 %) faster — a partition change
-    re-seeds the per-pixel RNG states and may grow buffers, so it must stay rare once the split has settled. The frame that
-    follows a move pays for exactly that and is therefore not used as a measurement (`due()` is False for it)."""
+    moves the edges only when the predicted slowest strip gets at least `gain` (default 8 %; twice that once the split has
+    settled) faster. A move is cheap — generator states are per global pixel and scratch is sized for the full frame, so nothing
+    is re-seeded or reallocated — but it restarts the mesh layer's temporal blend, so the frame that follows a move is not used
+    as a measurement (`due()` is False for it)."""
 
     def __init__(self, width, world, halo, align=1, gain=0.08):
         self.width, self.world, self.halo, self.align, self.gain = width, world, halo, align, gain
@@ -156,7 +157,8 @@ class StripBalancer:
 
     def observe(self, col_cost):
         new = balanced_bounds(col_cost, self.world, self.align, self.min_width)
-        if new != self.bounds and self._slowest(col_cost, new) < (1.0 - self.gain) * self._slowest(col_cost, self.bounds):
+        gain = self.gain if self.frames < 16 else 2.0 * self.gain
+        if new != self.bounds and self._slowest(col_cost, new) < (1.0 - gain) * self._slowest(col_cost, self.bounds):
             self.bounds = new
             self.changes += 1
             self.cooldown = 2          # tick() of this frame takes one off: the NEXT frame is the one skipped
