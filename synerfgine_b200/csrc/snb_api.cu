@@ -53,6 +53,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		else return c->fail(SNB_ERR_ARG, "mlp: expected mma | tc");
 	} else if (k == "overlap") {
 		c->overlap_layers = v != "0";
+	} else if (k == "mesh_priority") {
+		c->mesh_priority = v == "high" ? 1 : v == "low" ? -1 : 0;
 	} else if (k == "bands") {
 		c->bands = v == "2" ? 2 : 1;
 	} else if (k == "dead_terms") {
@@ -81,6 +83,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
 	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
 	if (const char* mv = getenv("SNB_BANDS")) snb_set_option(c, "bands", mv);
+	if (const char* mv = getenv("SNB_MESH_PRIORITY")) snb_set_option(c, "mesh_priority", mv);
 	if (cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_band0, cudaEventDisableTiming) != cudaSuccess ||
 	    cudaEventCreateWithFlags(&c->ev_band1, cudaEventDisableTiming) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;

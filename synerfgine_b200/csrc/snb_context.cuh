@@ -85,6 +85,7 @@ struct snb_ctx {
 	int bands = 1;                                          // option "bands": 2 was measured slower (7.18 vs 6.97 ms), kept for A/B
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_layers = true;
+	int mesh_priority = 0;         // stream priority of the mesh layer's stream: +1 high, 0 default, -1 low (option "mesh_priority")
 	bool skip_dead_terms = true;   // k_nerf_shadow_terms: skip terms no written pixel can observe (option "dead_terms")
 
 	int fail(int code, const std::string& msg) { err = msg; return code; }

@@ -282,7 +282,10 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 	const bool fork = c->overlap_layers && rt->show_nerf;
 	if (fork) {
 		if (!c->stream2) {
-			SNB_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+			int prio_lo = 0, prio_hi = 0;   // numerically lower = higher priority
+			SNB_CUDA(c, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+			const int prio = c->mesh_priority > 0 ? prio_hi : c->mesh_priority < 0 ? prio_lo : 0;
+			SNB_CUDA(c, cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio));
 			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
 			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
 		}
