@@ -168,6 +168,10 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	d.env.min_mip = 0; d.env.max_mip = m->max_cascade;
 	d.env.render_aabb.lo = ld3(m->render_aabb_min); d.env.render_aabb.hi = ld3(m->render_aabb_max);
 	d.env.to_local = ldm3(m->render_aabb_to_local);
+	{
+		static const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+		d.env.local_identity = std::memcmp(m->render_aabb_to_local, ident, sizeof ident) == 0 ? 1u : 0u;   // bitwise: -0 entries do not qualify
+	}
 	d.env.st = make_stepping(m->cone_angle_constant);
 	// coarse look-ahead grid over the extent of cascade max_cascade (snb_march.cuh)
 	d.env.coarse = nullptr;

@@ -59,6 +59,7 @@ struct MarchEnv {
 	uint32_t min_mip, max_mip;
 	Aabb render_aabb;
 	m3 to_local;               // render_aabb_to_local
+	uint32_t local_identity;   // to_local is exactly the identity (set by snb_set_model): in_render_box skips the 3x3 product
 	Stepping st;
 	const uint32_t* coarse;    // kCoarseWords words or nullptr (no look-ahead)
 	v3 coarse_lo;              // world position of coarse cell (0,0,0)
@@ -208,6 +209,12 @@ SNB_HD bool coarse_clear_ahead(v3 pos, v3 d, const MarchEnv& env) {
 	return false;
 }
 
+// m_render_aabb.contains(render_aabb_to_local * pos). With the identity the product is pos itself bit for bit:
+// (1*x + 0*y) + 0*z == x for finite coordinates (a -0 may become +0, which no comparison sees), so it is skipped.
+SNB_HD bool in_render_box(v3 pos, const MarchEnv& env) {
+	return env.render_aabb.contains(env.local_identity ? pos : mul(env.to_local, pos));
+}
+
 SNB_HD bool env_cell_occupied(v3 pos, const MarchEnv& env, uint32_t mip) {
 #ifdef __CUDA_ARCH__
 	return cell_occupied_xyz(pos, env.bits_xyz, mip);
@@ -227,7 +234,7 @@ SNB_HD float skip_to_occupied(float t, v3 o, v3 d, v3 idir, const MarchEnv& env)
 	int n_empty = 0;
 	while (true) {
 		const v3 pos = o + d * t;
-		if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) return kMaxDepth;
+		if (t >= kMaxDepth || !in_render_box(pos, env)) return kMaxDepth;
 		uint32_t mip = clamp_mip(mip_of(pos), env);
 		if (!env.bitfield || env_cell_occupied(pos, env, mip)) return t;
 		if ((n_empty++ % kLookAheadEvery) == 0 && coarse_clear_ahead(pos, d, env)) return kMaxDepth;

@@ -88,7 +88,7 @@ k_nerf_march_tc(DevModel model, DevView view, NerfOut out, int render_mode, cons
 #pragma unroll 1
 			for (int step = 0; step < kTcSearchSteps; ++step) {
 				const v3 pos = o + d * t;
-				if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { finish(); break; }   // left the volume
+				if (t >= kMaxDepth || !in_render_box(pos, env)) { finish(); break; }   // left the volume
 				uint32_t mip = clamp_mip(mip_of(pos), env);
 				if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { searching = false; n_empty = 0; break; }
 				if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { finish(); break; }

@@ -257,7 +257,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			for (;;) {
 				if (searching) {
 					const v3 pos = o + d * t;
-					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { fin = true; searching = false; }   // left the volume
+					if (t >= kMaxDepth || !in_render_box(pos, env)) { fin = true; searching = false; }   // left the volume
 					else {
 						uint32_t mip = clamp_mip(mip_of(pos), env);
 						if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { valid = true; searching = false; n_empty = 0; }

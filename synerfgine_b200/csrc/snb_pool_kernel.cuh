@@ -155,7 +155,7 @@ k_nerf_march_pool(DevModel model, DevView view, NerfOut out, int render_mode, co
 #pragma unroll 1
 				for (int step = 0; step < kSearchSteps; ++step) {
 					const v3 pos = o + d * t;
-					if (t >= kMaxDepth || !env.render_aabb.contains(mul(env.to_local, pos))) { s = kSlotEmpty; break; }   // left the volume
+					if (t >= kMaxDepth || !in_render_box(pos, env)) { s = kSlotEmpty; break; }   // left the volume
 					uint32_t mip = clamp_mip(mip_of(pos), env);
 					if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { s = kSlotReady; n_empty = 0; break; }
 					if (((n_empty++) & (uint32_t)(kLookAheadEvery - 1)) == 0u && coarse_clear_ahead(pos, d, env)) { s = kSlotEmpty; break; }
@@ -240,7 +240,7 @@ k_nerf_march_pool(DevModel model, DevView view, NerfOut out, int render_mode, co
 				// probe the next cell here (the ray is in registers): READY again if it is occupied, else SEARCH
 				const v3 npos = o + d * t;
 				uint32_t s = kSlotSearch;
-				if (t < kMaxDepth && env.render_aabb.contains(mul(env.to_local, npos))) {
+				if (t < kMaxDepth && in_render_box(npos, env)) {
 					const uint32_t mip = clamp_mip(mip_of(npos), env);
 					if (!env.bitfield || cell_occupied_xyz(npos, env.bits_xyz, mip)) s = kSlotReady;
 				}
