@@ -28,6 +28,21 @@ def model(kind="fox16x2"):
     return _models[kind]
 
 
+def cropped_model():
+    """small16x2 with the GUI's crop box applied: a smaller render_aabb and a rotated render_aabb_to_local (the general
+    m_render_aabb.contains(m_render_aabb_to_local * pos) path; every other model here has the identity)."""
+    import copy
+    import math
+    if "cropped" not in _models:
+        m = copy.copy(model("small16x2"))
+        a = math.radians(25.0)
+        c, s_ = np.float32(math.cos(a)), np.float32(math.sin(a))
+        m.render_aabb_to_local = [float(c), float(s_), 0.0, float(-s_), float(c), 0.0, 0.0, 0.0, 1.0]      # column-major rotation about z
+        m.render_aabb_min, m.render_aabb_max = [-0.2, -0.4, -0.3], [1.0, 0.75, 1.2]
+        _models["cropped"] = m
+    return _models["cropped"]
+
+
 def camera_matrix(view=(-0.30, -0.45, -0.84), at=(0.5, 0.42, 0.5), zoom=1.0):
     lib = _lib.load()
     out = np.zeros(12, np.float32)

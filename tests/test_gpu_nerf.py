@@ -35,9 +35,9 @@ def dev(shape, dtype):
 
 
 @pytest.mark.parametrize("kind,w,h,spp,snap", [("small16x2", 96, 64, 0, 1), ("small16x2", 64, 48, 3, 0), ("unit16x2", 64, 64, 0, 1), ("big16x2", 64, 64, 1, 0),
-                                                 ("noocc", 32, 32, 0, 1)])
+                                                 ("noocc", 32, 32, 0, 1), ("cropped", 96, 64, 0, 1), ("cropped", 64, 48, 2, 0)])
 def test_march_samples_bit_exact(snb, orc, ctx, kind, w, h, spp, snap):
-    m = common.model(kind)
+    m = common.cropped_model() if kind == "cropped" else common.model(kind)
     d = set_model(snb, ctx, m)
     cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
     v = common.make_view(w, h, cam=cam, spp=spp, snap=snap)
@@ -86,11 +86,12 @@ def test_network_hash_indices_and_outputs(snb, orc, ctx, kind, mlp):
     assert np.abs(b).max() > 0.1
 
 
-@pytest.mark.parametrize("kind,alt,w,h", [("small16x2", 0, 128, 96), ("small16x2", 1, 128, 96), ("fox8x4", 1, 64, 64), ("unit16x2", 0, 64, 64), ("big16x2", 1, 64, 64)])
+@pytest.mark.parametrize("kind,alt,w,h", [("small16x2", 0, 128, 96), ("small16x2", 1, 128, 96), ("fox8x4", 1, 64, 64), ("unit16x2", 0, 64, 64), ("big16x2", 1, 64, 64),
+                                          ("cropped", 1, 96, 64)])
 @pytest.mark.parametrize("march", ["lane", "pool", "tc"])
 def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
     """march: "lane" = one ray per lane + mma.sync MLPs, "pool" = warp ray pool, "tc" = MLPs on tcgen05/TMEM (CTA level)."""
-    m = common.model(kind)
+    m = common.cropped_model() if kind == "cropped" else common.model(kind)
     d = set_model(snb, ctx, m)
     assert snb.snb_set_option(ctx, b"march", march.encode()) == 0
     cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
