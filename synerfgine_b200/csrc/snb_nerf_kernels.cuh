@@ -20,8 +20,12 @@
 namespace snb {
 
 constexpr int kBatchSteps = 8;       // n_steps_between_compaction for <= 262144 alive rays (src/testbed_nerf.cu:2189-2190)
-constexpr int kFusedWarps = 4;
+#ifndef SNB_LANE_WARPS
+#define SNB_LANE_WARPS 8       // warps per CTA of the lane march (tuning hook; with 8, SNB_LANE_CTAS=2 keeps 16 warps / SM and halves the weight copies)
+#endif
+constexpr int kFusedWarps = SNB_LANE_WARPS;
 constexpr int kFusedThreads = kFusedWarps * 32;
+constexpr int kTapWarps = 4, kTapThreads = kTapWarps * 32;   // parity tap kernel (k_network_inference): fixed, static shared memory
 
 struct NerfCounters { unsigned long long samples, rays, hits, batches, iterations, dda_steps, net_phases, reserved; };
 
@@ -173,20 +177,23 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 // wait), (3) encode + both MLPs for the lanes that have a sample, (4) composite. A lane still searching after (2)
 // simply carries on in the next iteration, so one ray crossing a long empty gap no longer stalls the other 31.
 #ifndef SNB_LANE_CTAS
-#define SNB_LANE_CTAS 4     // resident CTAs per SM the register budget is set for (tuning hook)
+#define SNB_LANE_CTAS 2     // resident CTAs per SM the register budget is set for (tuning hook)
 #endif
 #ifndef SNB_LANE_MIN_FILL
 #define SNB_LANE_MIN_FILL 20   // lanes holding a sample before the network runs (tuning hook)
 #endif
 constexpr int kMinFill = SNB_LANE_MIN_FILL;
+constexpr int kLaneSmemBytes = kFragWords * 4 + kFusedWarps * kWarpSmemBytes + (int)sizeof(LevelDesc) * kMaxLevels + kCoarseWords * 4;
 template <int F, bool ALT>
 __global__ void __launch_bounds__(kFusedThreads, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
                    unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
-	__shared__ __align__(16) uint32_t s_w[kFragWords];
-	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
-	__shared__ LevelDesc s_levels[kMaxLevels];
-	__shared__ uint32_t s_coarse[kCoarseWords];   // look-ahead occupancy (4 KB)
+	// dynamic shared memory (kLaneSmemBytes): [fragment-ordered weights | per-warp staging + output tiles | level table | look-ahead grid]
+	extern __shared__ __align__(16) unsigned char s_lane[];
+	uint32_t* s_w = reinterpret_cast<uint32_t*>(s_lane);
+	unsigned char (*s_warp)[kWarpSmemBytes] = reinterpret_cast<unsigned char (*)[kWarpSmemBytes]>(s_lane + kFragWords * 4);
+	LevelDesc* s_levels = reinterpret_cast<LevelDesc*>(s_lane + kFragWords * 4 + kFusedWarps * kWarpSmemBytes);
+	uint32_t* s_coarse = reinterpret_cast<uint32_t*>(s_lane + kFragWords * 4 + kFusedWarps * kWarpSmemBytes + sizeof(LevelDesc) * kMaxLevels);   // look-ahead occupancy (4 KB)
 	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += kFusedThreads) s_coarse[i] = __ldg(model.env.coarse + i);
 	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
@@ -374,12 +381,12 @@ __global__ void __launch_bounds__(128) k_march_trace(DevView view, MarchEnv env,
 
 // NerfNetwork inference on explicit NerfCoordinates (n x 7 floats) through the same encode + warp evaluator as the fused kernel.
 template <int F>
-__global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel model, const float* __restrict__ coords, uint64_t n, uint16_t* __restrict__ out,
+__global__ void __launch_bounds__(kTapThreads) k_network_inference(DevModel model, const float* __restrict__ coords, uint64_t n, uint16_t* __restrict__ out,
                                                                      uint16_t* __restrict__ features, uint32_t* __restrict__ hash_idx) {
 	__shared__ __align__(16) uint32_t s_w[kFragWords];
-	__shared__ __align__(16) unsigned char s_warp[kFusedWarps][kWarpSmemBytes];
+	__shared__ __align__(16) unsigned char s_warp[kTapWarps][kWarpSmemBytes];
 	__shared__ LevelDesc s_levels[kMaxLevels];
-	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
+	for (int i = threadIdx.x; i < kFragWords / 4; i += kTapThreads)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
 	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x, model.grid_params);
 	__syncthreads();
@@ -388,7 +395,7 @@ __global__ void __launch_bounds__(kFusedThreads) k_network_inference(DevModel mo
 	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
 	__half* row = tile + lane * kTileStrideH;
 	const uint64_t n_tiles = (n + 31) / 32;
-	for (uint64_t tile_i = (uint64_t)blockIdx.x * kFusedWarps + warp; tile_i < n_tiles; tile_i += (uint64_t)gridDim.x * kFusedWarps) {
+	for (uint64_t tile_i = (uint64_t)blockIdx.x * kTapWarps + warp; tile_i < n_tiles; tile_i += (uint64_t)gridDim.x * kTapWarps) {
 		const uint64_t i = tile_i * 32 + lane;
 		const bool valid = i < n;
 		uint32_t sh[8];

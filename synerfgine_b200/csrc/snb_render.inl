@@ -24,12 +24,13 @@ static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int r
 	if (c->march_variant == 3) {   // previous form (one ray per lane), kept for A/B measurements: SNB_MARCH=v3
 		static int per_sm = 0;   // per template instance
 		if (per_sm == 0) {
-			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, 0));
+			SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kLaneSmemBytes));
+			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, kLaneSmemBytes));
 			per_sm = std::max(1, per_sm);
 		}
 		c->fused_blocks_per_sm = per_sm;
 		const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + kFusedThreads - 1) / kFusedThreads));
-		k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+		k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, kLaneSmemBytes, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
 		SNB_LAUNCHED(c);
 		return SNB_OK;
 	}

@@ -72,12 +72,12 @@ int snb_network_inference(snb_ctx* c, const float* coords_dev, uint64_t n, uint1
 		return SNB_OK;
 	}
 	const uint64_t tiles = (n + 31) / 32;
-	const int blocks = (int)std::min<uint64_t>((tiles + kFusedWarps - 1) / kFusedWarps, (uint64_t)c->sm_count * 8);
+	const int blocks = (int)std::min<uint64_t>((tiles + kTapWarps - 1) / kTapWarps, (uint64_t)c->sm_count * 8);
 	switch (c->feat_per_level) {
-		case 1: k_network_inference<1><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
-		case 2: k_network_inference<2><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
-		case 4: k_network_inference<4><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
-		default: k_network_inference<8><<<blocks, kFusedThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		case 1: k_network_inference<1><<<blocks, kTapThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		case 2: k_network_inference<2><<<blocks, kTapThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		case 4: k_network_inference<4><<<blocks, kTapThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
+		default: k_network_inference<8><<<blocks, kTapThreads, 0, c->stream>>>(c->model, coords_dev, n, out_dev, features_dev, hash_idx_dev); break;
 	}
 	SNB_LAUNCHED(c);
 	return SNB_OK;
