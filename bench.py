@@ -279,6 +279,19 @@ def run_ours(args, rank, local_rank, world):
             dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
         e2e_s = float(e2e_s.item())
 
+        # ---- the march kernel without the mesh layer running beside it (same frames, overlap off): explains `roofline` ----
+        march_alone_ms = None
+        if world == 1:
+            lib.snb_set_option(ctx, b"overlap", b"0")
+            alone = []
+            for i in range(2 + 5):
+                flush.zero_()
+                one_frame(); stream.synchronize()
+                if i >= 2:
+                    alone.append(tb.stage_ms()["nerf_march"])
+            lib.snb_set_option(ctx, b"overlap", b"1")
+            march_alone_ms = float(np.mean(alone))
+
         # ---- present stage, timed on its own: FXAA blit of the final frame into an RGB8 window image ----
         present = None
         if world == 1:
@@ -324,7 +337,9 @@ def run_ours(args, rank, local_rank, world):
             "clocks": clocks,
             "roofline": {"kernel": "k_nerf_march_fused", "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
                          "peak_source": f"{src} (MEASURED_PEAKS.json hbm_gbs)", "launch_ms": mm,
-                         "launch_ms_note": "CUDA events around the march launch on the context stream; the mesh layer runs concurrently on the second stream (SNB_OVERLAP=0: 4.13 ms alone)",
+                         "launch_ms_note": "CUDA events around the march launch on the context stream; the mesh layer runs concurrently on the second stream",
+                         "alone": ({"launch_ms": march_alone_ms, "achieved": algo_bytes / (march_alone_ms * 1e-3) / 1e9, "frac": algo_bytes / (march_alone_ms * 1e-3) / 1e9 / hbm,
+                                    "note": "same kernel, same frames, mesh layer not overlapped (option overlap=0)"} if march_alone_ms else None),
                          "note": "algorithmic bytes = samples x 512 B hash gather + rays x 64 B; the 24 MB table is L2-resident by design, so DRAM traffic << algorithmic bytes",
                          "tensor": {"achieved_tflops": samples / K * FLOP_PER_SAMPLE / (mm * 1e-3) / 1e12, "peak_tflops": tflops}},
         }
