@@ -21,7 +21,7 @@ namespace snb {
 
 constexpr int kBatchSteps = 8;       // n_steps_between_compaction for <= 262144 alive rays (src/testbed_nerf.cu:2189-2190)
 #ifndef SNB_LANE_WARPS
-#define SNB_LANE_WARPS 8       // warps per CTA of the lane march (tuning hook; with 8, SNB_LANE_CTAS=2 keeps 16 warps / SM and halves the weight copies)
+#define SNB_LANE_WARPS 10      // warps per CTA of the lane march (tuning hook): 2 CTAs x 10 warps = 20 warps / SM at 96 registers, one 20 KB weight copy per CTA
 #endif
 constexpr int kFusedWarps = SNB_LANE_WARPS;
 constexpr int kFusedThreads = kFusedWarps * 32;
