@@ -29,7 +29,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOAD = "C2: 1920x1080 fox-architecture NeRF (16x2 hash grid, T=2^19, 64-wide MLPs) + armadillo.obj lambertian + 1 point light, nerf_shadow_samples=4, syn_shadow_samples=2"
 BYTES_PER_SAMPLE = 512          # hash gather: 16 levels x 8 corners x 2 features x 2 B
-BYTES_PER_RAY = 32 + 20 + 12    # queue record read + rgba/depth write + position write
+BYTES_PER_RAY = 64 + 20 + 12    # queue record read (ray + its SH-4 block) + rgba/depth write + position write
 FLOP_PER_SAMPLE = 20480         # both MLPs, padded
 
 

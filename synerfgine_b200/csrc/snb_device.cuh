@@ -67,10 +67,12 @@ struct DevScene {
 	const DevLight* lights; uint32_t n_lights;
 };
 
-struct RayRec {                  // 32 B: one queue entry produced by ray generation
+struct RayRec {                  // 64 B: one queue entry produced by ray generation
 	float ox, oy, oz, t;
 	float dx, dy, dz;
 	uint32_t idx;                // global pixel index x + width * y
+	uint32_t sh[8];              // SH-4 encoding of the direction (16 halves): computed once per ray where the ray is made, so
+	                             // the march's refill path is a 32-byte copy instead of ~150 instructions in its hot loop
 };
 
 } // namespace snb

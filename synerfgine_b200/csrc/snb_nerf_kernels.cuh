@@ -147,6 +147,10 @@ __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env,
 		float4* q = reinterpret_cast<float4*>(queue + base + __popc(mask & ((1u << lane) - 1u)));
 		q[0] = make_float4(rec.ox, rec.oy, rec.oz, rec.t);
 		q[1] = make_float4(rec.dx, rec.dy, rec.dz, __uint_as_float(rec.idx));
+		uint32_t sh[8];
+		encode_direction_sh4((mk3(rec.dx, rec.dy, rec.dz) + 1.0f) * 0.5f, sh);   // warp_direction, nerf_device.cuh:290-292
+		reinterpret_cast<uint4*>(q)[2] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+		reinterpret_cast<uint4*>(q)[3] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
 	}
 }
 
@@ -248,9 +252,10 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				idir = 1.0f / d;
 				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; n_empty = 0; alive = true;
 				++n_launched;
-				uint32_t sh[8];
-				encode_direction_sh4((d + 1.0f) * 0.5f, sh);   // warp_direction, nerf_device.cuh:290-292
-				stage_sh_row(tile, lane, sh);
+				// SH block of the staged row (k-tile 2): encoded by ray generation, copied as is
+				const uint4 s0 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 2), s1 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 3);
+				uint4* dst = reinterpret_cast<uint4*>(tile + lane * kTileStrideH + kTileShCol);
+				dst[0] = s0; dst[1] = s1;
 			}
 			if (base + __popc(need) >= n_rays) drained = true;
 		}
