@@ -290,3 +290,18 @@ def test_snapshot_file_round_trip_renders_the_same_frame(snb, tmp_path):
     with pytest.raises(RuntimeError):
         b.load_snapshot(tmp_path / "missing.ingp")
     b.close(); c.close()
+
+
+def test_large_frame_4k(snb, ctx):
+    """Maximum size the reference's GUI offers (4K): buffers grow, 32-bit indexing holds (8.3 M pixels x 16 B rows, queue of
+    64 B records), and a tile in the far corner still equals the crop of the full frame."""
+    from synerfgine_b200._lib import Tile
+    m = common.model("small16x2")
+    set_model(snb, ctx, m)
+    W, H = 3840, 2160
+    v = common.make_view(W, H, spp=0, snap=1)
+    fb, depth, pos, cnt = _render_full(snb, ctx, v)
+    assert bool(torch.isfinite(fb).all()) and cnt[1] > 100_000 and (fb[..., 3] > 0.5).float().mean() > 0.05
+    t = Tile(W - 517, H - 301, 517, 301)
+    pfb, pdepth, ppos, _ = _render_full(snb, ctx, v, tile=t)
+    assert torch.equal(pfb, fb[t.y0:, t.x0:]) and torch.equal(pdepth, depth[t.y0:, t.x0:]) and torch.equal(ppos, pos[t.y0:, t.x0:])
