@@ -173,8 +173,10 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 }
 
 // ---- the persistent fused kernel -----------------------------------------------------------------------------------
-// grid = SMs x resident CTAs, block = 4 warps; smem = fragment-ordered MLP weights (20 KB, shared by the CTA) +
-// per-warp staging tile (3.5 KB) + per-warp output tile (256 B) + level table (1 KB) + look-ahead grid (4 KB).
+// grid = SMs x SNB_LANE_CTAS (2), block = SNB_LANE_WARPS (10) warps; dynamic smem (kLaneSmemBytes, 62 KB) = fragment-ordered
+// MLP weights (20 KB, shared by the CTA's warps) + per-warp staging tile (3.5 KB) + per-warp output tile (256 B) + level
+// table (1 KB) + look-ahead grid (4 KB). Warps never synchronise after the prologue; the CTA shape only sets how many warps
+// share one weight copy and thereby how much of the SM's 256 KB is left as L1 for the gathers (profiles/r01_ncu_fused_v3.md).
 //
 // One loop iteration of a warp = (1) refill finished slots from the queue, (2) search phase: lanes whose ray sits in
 // empty space take DDA steps until at least kMinFill lanes hold a sample position (lanes that already have one
