@@ -209,6 +209,17 @@ SNB_HD bool coarse_clear_ahead(v3 pos, v3 d, const MarchEnv& env) {
 	return false;
 }
 
+#ifdef __CUDACC__
+// Out-of-line twin of coarse_clear_ahead for the persistent march kernel (instruction-cache budget): the walk runs once per
+// kLookAheadEvery empty cells per ray, its ~150 instructions need not sit inside the hot loop. `coarse` may point to shared memory.
+__device__ __noinline__ bool coarse_clear_ahead_call(float px, float py, float pz, float dx, float dy, float dz, const uint32_t* coarse, float lox, float loy, float loz,
+                                                     float inv_cell) {
+	MarchEnv e;
+	e.coarse = coarse; e.coarse_lo = mk3(lox, loy, loz); e.coarse_inv_cell = inv_cell;
+	return coarse_clear_ahead(mk3(px, py, pz), mk3(dx, dy, dz), e);
+}
+#endif
+
 // m_render_aabb.contains(render_aabb_to_local * pos). With the identity the product is pos itself bit for bit:
 // (1*x + 0*y) + 0*z == x for finite coordinates (a -0 may become +0, which no comparison sees), so it is skipped.
 SNB_HD bool in_render_box(v3 pos, const MarchEnv& env) {

@@ -275,7 +275,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 					else {
 						uint32_t mip = clamp_mip(mip_of(pos), env);
 						if (!env.bitfield || cell_occupied_xyz(pos, env.bits_xyz, mip)) { valid = true; searching = false; n_empty = 0; }
-						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead(pos, d, env)) { fin = true; searching = false; }
+						else if (((n_empty++) & (kLookAheadEvery - 1)) == 0 && coarse_clear_ahead_call(pos.x, pos.y, pos.z, d.x, d.y, d.z, env.coarse, env.coarse_lo.x, env.coarse_lo.y, env.coarse_lo.z, env.coarse_inv_cell)) { fin = true; searching = false; }
 						else {
 							while (mip < env.max_mip && !cell_occupied_xyz(pos, env.bits_xyz, mip + 1)) ++mip;
 							t = advance_past_voxel_call(t, env.st, pos, d, idir, mip);
