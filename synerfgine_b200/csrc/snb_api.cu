@@ -57,6 +57,14 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		c->mesh_priority = v == "high" ? 1 : v == "low" ? -1 : 0;
 	} else if (k == "bands") {
 		c->bands = v == "2" ? 2 : 1;
+	} else if (k == "terms_compact") {
+		c->terms_compact = v != "0";
+	} else if (k == "mesh_after") {
+		c->mesh_after_raygen = v == "raygen";
+	} else if (k == "sng_block" || k == "terms_block") {
+		const int b = atoi(v.c_str());
+		if (b != 0 && b != 32 && b != 64 && b != 128) return c->fail(SNB_ERR_ARG, "sng_block / terms_block: expected 0 | 32 | 64 | 128");
+		(k == "sng_block" ? c->sng_block : c->terms_block) = b;
 	} else if (k == "dead_terms") {
 		c->skip_dead_terms = v != "0";
 	} else return c->fail(SNB_ERR_ARG, "unknown option");
@@ -82,6 +90,10 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
 	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
 	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
+	if (const char* mv = getenv("SNB_TERMS_COMPACT")) snb_set_option(c, "terms_compact", mv);
+	if (const char* mv = getenv("SNB_MESH_AFTER")) snb_set_option(c, "mesh_after", mv);
+	if (const char* mv = getenv("SNB_SNG_BLOCK")) snb_set_option(c, "sng_block", mv);
+	if (const char* mv = getenv("SNB_TERMS_BLOCK")) snb_set_option(c, "terms_block", mv);
 	if (const char* mv = getenv("SNB_BANDS")) snb_set_option(c, "bands", mv);
 	if (const char* mv = getenv("SNB_MESH_PRIORITY")) snb_set_option(c, "mesh_priority", mv);
 	if (cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_band0, cudaEventDisableTiming) != cudaSuccess ||

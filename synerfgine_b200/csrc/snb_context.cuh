@@ -66,7 +66,7 @@ struct snb_ctx {
 	snb::DevBuf d_syn_origins, d_syn_dirs, d_syn_rgba, d_syn_depth;
 	bool syn_reset = true;
 	int syn_w = 0, syn_h = 0;
-	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
+	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_terms_list, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
 	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused), 4 = ray pool (snb_pool_kernel.cuh), 5 = tcgen05 MLPs (snb_march_tc_kernel.cuh)
@@ -85,7 +85,12 @@ struct snb_ctx {
 	int bands = 1;                                          // option "bands": 2 was measured slower (7.18 vs 6.97 ms), kept for A/B
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_layers = true;
-	int mesh_priority = 0;         // stream priority of the mesh layer's stream: +1 high, 0 default, -1 low (option "mesh_priority")
+	int mesh_priority = 1;         // stream priority of the mesh layer's stream: +1 high (default: the mesh layer finishes under ray generation and the march runs undisturbed), 0 default, -1 low (option "mesh_priority")
+	bool mesh_after_raygen = false;   // fork the mesh layer behind NeRF ray generation instead of at frame start (option "mesh_after" = "raygen")
+	const void* deferred_syn_view = nullptr; const snb_rt_params* deferred_syn_rt = nullptr;   // set by snb_frame for the duration of one render_nerf_layer call
+	int sng_block = 128;           // k_raytrace: threads per block with a warp = 8 x 4 pixels; 0 = row-linear mapping (option "sng_block")
+	int terms_block = 0;           // k_nerf_shadow_terms: same choice (option "terms_block"); row-linear measured faster there
+	bool terms_compact = false;    // observable pixels queued by k_nerf_shadow_classify, k_nerf_shadow_terms over the queue with full warps (option "terms_compact"); measured slower on C2 (post 0.65 against 0.60 ms: the divergence is inside the BVH / DDA work, not in who does it), so off
 	bool skip_dead_terms = true;   // k_nerf_shadow_terms: skip terms no written pixel can observe (option "dead_terms")
 
 	int fail(int code, const std::string& msg) { err = msg; return code; }

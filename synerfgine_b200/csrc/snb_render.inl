@@ -81,6 +81,7 @@ static int launch_fused_f(snb_ctx* c, const DevView& dv, const NerfOut& out, int
 // depend on the split (rays are independent; normals and shadows run afterwards on the whole tile). Measured on C2: 7.18 ms
 // per frame against 6.97 ms with one band — two half-sized persistent marches lose more in ramp-up and tail than the
 // overlap wins — so the default is one band; the option stays for A/B runs.
+static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, cudaStream_t st);
 static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render_mode, float* fb, float* depth, float* positions) {
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	const int n_px = dv.tw * dv.th;
@@ -99,6 +100,13 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	k_nerf_raygen<<<(split + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, split);
 	SNB_LAUNCHED(c);
 	c->stage_end(0);
+	if (c->deferred_syn_view) {   // option "mesh_after" = "raygen": the mesh layer is forked here, behind ray generation
+		const DevView* sv = static_cast<const DevView*>(c->deferred_syn_view); c->deferred_syn_view = nullptr;
+		SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+		SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+		const int rc2 = render_syn_layer(c, *sv, c->deferred_syn_rt, c->stream2); if (rc2) return rc2;
+		SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+	}
 	if (two) {
 		SNB_CUDA(c, cudaEventRecord(c->ev_band0, c->stream));
 		SNB_CUDA(c, cudaStreamWaitEvent(c->stream3, c->ev_band0, 0));
@@ -147,7 +155,7 @@ static RtParams make_rt(const snb_rt_params* rt) {
 }
 
 // Mesh layer into the context's syn buffers (tile-sized).
-static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, cudaStream_t st = nullptr) {
+static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, cudaStream_t st) {
 	if (!st) st = c->stream;
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	if (rt->samples == 0 || rt->bounces == 0 || rt->shadow_iters == 0) return c->fail(SNB_ERR_ARG, "samples, bounces and shadow_iters must be >= 1");
@@ -164,8 +172,10 @@ static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* 
 		SNB_LAUNCHED(c);
 		c->syn_reset = false;
 	}
-	k_raytrace<<<(n + 127) / 128, 128, 0, st>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
-	                                                   c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>(), dv.width, dv.tx0, dv.ty0, dv.tw);
+	const int sb = c->sng_block;   // 0 = row-linear 128-thread blocks; else threads per block of the 8 x 4-patch-per-warp mapping
+	const dim3 grid_px = sb ? dim3(((dv.tw + 7) / 8 + sb / 32 - 1) / (sb / 32), (dv.th + 3) / 4) : dim3((n + 127) / 128);
+	k_raytrace<<<grid_px, sb ? sb : 128, 0, st>>>(n, c->d_syn_origins.as<float>(), c->d_syn_dirs.as<float>(), dv.cam.c0, c->model.env, c->scene, make_rt(rt),
+	                                              c->d_rng_syn.as<Rng>(), c->d_syn_rgba.as<float4>(), c->d_syn_depth.as<float>(), dv.width, dv.tx0, dv.ty0, dv.tw, sb);
 	SNB_LAUNCHED(c);
 	c->stage_end(3, st);
 	return SNB_OK;
@@ -181,10 +191,23 @@ static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int
 		const uint32_t n = (uint32_t)(dv.tw * dv.th);
 		SNB_CUDA(c, c->d_terms.reserve((size_t)n * 4));
 		MarchEnv env = c->model.env; env.min_mip = 0;
-		k_nerf_shadow_terms<<<(n + 127) / 128, 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
+		const int sb = c->terms_block;
+		const dim3 grid_px = sb ? dim3(((dv.tw + 7) / 8 + sb / 32 - 1) / (sb / 32), (dv.th + 3) / 4) : dim3((n + 127) / 128);
+		const float4* layer = (render_mode != 8 && c->skip_dead_terms) ? reinterpret_cast<const float4*>(fb) : nullptr;
+		const uint32_t* list = nullptr; uint32_t* list_count = nullptr;
+		if (layer && c->terms_compact) {
+			SNB_CUDA(c, c->d_terms_list.reserve((size_t)n * 4));
+			list_count = c->d_qctl.as<unsigned int>() + 8;
+			SNB_CUDA(c, cudaMemsetAsync(list_count, 0, 4, c->stream));
+			k_nerf_shadow_classify<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->scene, c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(), layer, dv.tw, dv.th,
+			                                                              rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0, c->d_terms_list.as<uint32_t>(), list_count);
+			SNB_LAUNCHED(c);
+			list = c->d_terms_list.as<uint32_t>(); layer = nullptr;
+		}
+		k_nerf_shadow_terms<<<list ? dim3((n + 127) / 128) : grid_px, (sb && !list) ? sb : 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
 		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(),
-		                                                            (render_mode != 8 && c->skip_dead_terms) ? reinterpret_cast<const float4*>(fb) : nullptr, dv.tw, dv.th,
-		                                                            rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0);
+		                                                            layer, dv.tw, dv.th,
+		                                                            rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0, sb, list, list_count);
 		SNB_LAUNCHED(c);
 		k_nerf_shadow_apply<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, rt->nerf_shadow_kernel / 2, rt->nerf_shadow_intensity, render_mode, c->d_terms.as<float>(),
 		                                                  reinterpret_cast<float4*>(fb), nullptr);
@@ -220,7 +243,7 @@ int snb_render_syn(snb_ctx* c, const snb_view* view, const snb_tile* tile, const
 	const DevView dv = make_view(view, tile);
 	const int scale = std::max(1, rt->syn_px_scale);
 	rc = ensure_rng(c, dv, nerf_view_of(dv, scale)); if (rc) return rc;
-	rc = render_syn_layer(c, dv, rt); if (rc) return rc;
+	rc = render_syn_layer(c, dv, rt, nullptr); if (rc) return rc;
 	const size_t n = (size_t)dv.tw * dv.th;
 	if (syn_rgba) SNB_CUDA(c, cudaMemcpyAsync(syn_rgba, c->d_syn_rgba.p, n * 16, cudaMemcpyDeviceToDevice, c->stream));
 	if (syn_depth) SNB_CUDA(c, cudaMemcpyAsync(syn_depth, c->d_syn_depth.p, n * 4, cudaMemcpyDeviceToDevice, c->stream));
@@ -290,18 +313,26 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
 			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
 		}
-		SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-		SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
 	}
-	rc = render_syn_layer(c, syn, rt, fork ? c->stream2 : c->stream); if (rc) return rc;
-	if (fork) SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+	const bool defer = fork && c->mesh_after_raygen;
+	if (defer) { c->deferred_syn_view = &syn; c->deferred_syn_rt = rt; }
+	else {
+		if (fork) {
+			SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+			SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+		}
+		rc = render_syn_layer(c, syn, rt, fork ? c->stream2 : c->stream); if (rc) return rc;
+		if (fork) SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+	}
 	// 2. NeRF layer with mesh shadows (Testbed::render sng overload)
 	SNB_CUDA(c, c->d_nerf_fb.reserve(n_nerf * 16));
 	SNB_CUDA(c, c->d_nerf_depth.reserve(n_nerf * 4));
 	if (rt->show_nerf) {
 		SNB_CUDA(c, c->d_positions.reserve(n_nerf * 12));
 		SNB_CUDA(c, c->d_normals.reserve(n_nerf * 12));
-		rc = render_nerf_layer(c, nerf, true, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), c->d_positions.as<float>()); if (rc) return rc;
+		rc = render_nerf_layer(c, nerf, true, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), c->d_positions.as<float>());
+		c->deferred_syn_view = nullptr;
+		if (rc) return rc;
 		rc = nerf_post(c, nerf, rt, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_positions.as<float>(), c->d_normals.as<float>()); if (rc) return rc;
 	}
 	if (fork) SNB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));

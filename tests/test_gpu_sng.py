@@ -179,6 +179,49 @@ def test_dead_shadow_terms_skip_is_result_identical(snb):
     assert (on[0][0][..., 3] > 0).mean() > 0.05 and (on[0][0][..., 3] == 0).mean() > 0.05   # the frame has both kinds of pixels
 
 
+@pytest.mark.parametrize("opts", [{b"sng_block": b"0", b"terms_block": b"0", b"mesh_priority": b"default", b"terms_compact": b"1"},
+                                  {b"terms_compact": b"1", b"terms_block": b"32"},
+                                  {b"sng_block": b"32", b"terms_block": b"64"},
+                                  {b"sng_block": b"128", b"terms_block": b"128", b"mesh_after": b"raygen"}])
+def test_pixel_mapping_and_scheduling_options_are_result_identical(snb, opts):
+    """A warp of k_raytrace / k_nerf_shadow_terms covers an 8 x 4 pixel patch (options "sng_block" / "terms_block"; "0" = 32
+    pixels of a row); "terms_compact" queues the observable pixels of the shadow-term pass and runs
+    full warps over the queue; "mesh_priority" / "mesh_after" only move the mesh layer in time. Pixels are independent, so three
+    consecutive frames (later ones depend on the generator states left by earlier ones) must have the same bits as the
+    defaults — on a frame whose width and height are not multiples of the patch."""
+    from synerfgine_b200 import Engine, Testbed
+
+    def run(options):
+        tb = Testbed(0)
+        for k, v in options.items():
+            assert tb.lib.snb_set_option(tb.ctx, k, v) == 0
+        tb.set_model(common.model("small16x2"))
+        eng = Engine()
+        eng.set_virtual_world_json(scenes.scene_json("c2"), scenes.mesh_dir())
+        eng.init(101, 67, tb)
+        frames = []
+        for _ in range(3):
+            a, d = eng.frame()
+            frames.append((a.cpu().numpy().copy(), d.cpu().numpy().copy()))
+        tb.close()
+        return frames
+
+    base, other = run({}), run(opts)
+    for (a, da), (b, db) in zip(base, other):
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+        np.testing.assert_array_equal(da.view(np.uint32), db.view(np.uint32))
+    assert (base[0][0][..., 3] > 0).mean() > 0.05
+
+
+def test_block_options_reject_bad_values(snb):
+    from synerfgine_b200 import Testbed
+    tb = Testbed(0)
+    assert tb.lib.snb_set_option(tb.ctx, b"sng_block", b"48") != 0
+    assert tb.lib.snb_set_option(tb.ctx, b"terms_block", b"256") != 0
+    assert tb.lib.snb_set_option(tb.ctx, b"sng_block", b"64") == 0
+    tb.close()
+
+
 # ---- present stage (SURVEY §8f rank 1): bytes equal the oracle's -----------------------------------------------------------
 @pytest.mark.parametrize("in_wh,out_wh", [((96, 64), (96, 64)), ((96, 64), (192, 128)), ((97, 61), (64, 48)), ((8, 8), (3, 5))])
 def test_present_bytes_match_oracle(snb, in_wh, out_wh):
