@@ -21,7 +21,7 @@ namespace snb {
 
 constexpr int kBatchSteps = 8;       // n_steps_between_compaction for <= 262144 alive rays (src/testbed_nerf.cu:2189-2190)
 #ifndef SNB_LANE_WARPS
-#define SNB_LANE_WARPS 10      // warps per CTA of the lane march (tuning hook): 2 CTAs x 10 warps = 20 warps / SM at 96 registers, one 20 KB weight copy per CTA
+#define SNB_LANE_WARPS 12      // warps per CTA of the lane march (tuning hook): 2 CTAs x 12 warps = 24 warps / SM at 80 registers, one 20 KB weight copy per CTA
 #endif
 constexpr int kFusedWarps = SNB_LANE_WARPS;
 constexpr int kFusedThreads = kFusedWarps * 32;
@@ -173,7 +173,7 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 }
 
 // ---- the persistent fused kernel -----------------------------------------------------------------------------------
-// grid = SMs x SNB_LANE_CTAS (2), block = SNB_LANE_WARPS (10) warps; dynamic smem (kLaneSmemBytes, 62 KB) = fragment-ordered
+// grid = SMs x SNB_LANE_CTAS (2), block = SNB_LANE_WARPS (12) warps; dynamic smem (kLaneSmemBytes, 70 KB) = fragment-ordered
 // MLP weights (20 KB, shared by the CTA's warps) + per-warp staging tile (3.5 KB) + per-warp output tile (256 B) + level
 // table (1 KB) + look-ahead grid (4 KB). Warps never synchronise after the prologue; the CTA shape only sets how many warps
 // share one weight copy and thereby how much of the SM's 256 KB is left as L1 for the gathers (profiles/r01_ncu_fused_v3.md).

@@ -21,7 +21,7 @@ static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
 
 template <int F, bool ALT>
 static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
-	if (c->march_variant == 3) {   // default ("lane"): one ray per lane, warp-level mma.sync MLPs, 2 CTAs x 10 warps per SM
+	if (c->march_variant == 3) {   // default ("lane"): one ray per lane, warp-level mma.sync MLPs, 2 CTAs x 12 warps per SM
 		static int per_sm = 0;   // per template instance
 		if (per_sm == 0) {
 			SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kLaneSmemBytes));
