@@ -57,6 +57,10 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		c->mesh_priority = v == "high" ? 1 : v == "low" ? -1 : 0;
 	} else if (k == "bands") {
 		c->bands = v == "2" ? 2 : 1;
+	} else if (k == "lane_warps") {
+		const int w = atoi(v.c_str());
+		if (w != 0 && w != kFusedWarpsFew && w != kFusedWarps) return c->fail(SNB_ERR_ARG, "lane_warps: expected 0 | 10 | 12");
+		c->lane_warps = w;
 	} else if (k == "terms_compact") {
 		c->terms_compact = v != "0";
 	} else if (k == "mesh_after") {
@@ -90,6 +94,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
 	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
 	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
+	if (const char* mv = getenv("SNB_LANE_WARPS")) snb_set_option(c, "lane_warps", mv);
 	if (const char* mv = getenv("SNB_TERMS_COMPACT")) snb_set_option(c, "terms_compact", mv);
 	if (const char* mv = getenv("SNB_MESH_AFTER")) snb_set_option(c, "mesh_after", mv);
 	if (const char* mv = getenv("SNB_SNG_BLOCK")) snb_set_option(c, "sng_block", mv);

@@ -88,6 +88,7 @@ struct snb_ctx {
 	int mesh_priority = 1;         // stream priority of the mesh layer's stream: +1 high (default: the mesh layer finishes under ray generation and the march runs undisturbed), 0 default, -1 low (option "mesh_priority")
 	bool mesh_after_raygen = false;   // fork the mesh layer behind NeRF ray generation instead of at frame start (option "mesh_after" = "raygen")
 	const void* deferred_syn_view = nullptr; const snb_rt_params* deferred_syn_rt = nullptr;   // set by snb_frame for the duration of one render_nerf_layer call
+	int lane_warps = 0;            // lane march CTA shape: 0 = chosen by tile size, 10 | 12 = forced (option "lane_warps")
 	int sng_block = 128;           // k_raytrace: threads per block with a warp = 8 x 4 pixels; 0 = row-linear mapping (option "sng_block")
 	int terms_block = 0;           // k_nerf_shadow_terms: same choice (option "terms_block"); row-linear measured faster there
 	bool terms_compact = false;    // observable pixels queued by k_nerf_shadow_classify, k_nerf_shadow_terms over the queue with full warps (option "terms_compact"); measured slower on C2 (post 0.65 against 0.60 ms: the divergence is inside the BVH / DDA work, not in who does it), so off

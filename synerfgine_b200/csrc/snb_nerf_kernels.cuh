@@ -189,19 +189,24 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 #define SNB_LANE_MIN_FILL 20   // lanes holding a sample before the network runs (tuning hook)
 #endif
 constexpr int kMinFill = SNB_LANE_MIN_FILL;
-constexpr int kLaneSmemBytes = kFragWords * 4 + kFusedWarps * kWarpSmemBytes + (int)sizeof(LevelDesc) * kMaxLevels + kCoarseWords * 4;
-template <int F, bool ALT>
-__global__ void __launch_bounds__(kFusedThreads, SNB_LANE_CTAS)
+// W = warps per CTA. Two shapes are built: kFusedWarps (12 warps, 80 registers: 24 warps / SM — the faster one when every lane
+// has several rays to work through, i.e. a full 1080p tile on one GPU) and kFusedWarpsFew (10 warps, 96 registers, no spills —
+// the faster one when a tile holds about one ray per lane and the march lasts as long as its longest rays: the N >= 2 strips).
+constexpr int kFusedWarpsFew = 10;
+constexpr int lane_smem_bytes(int w) { return kFragWords * 4 + w * kWarpSmemBytes + (int)sizeof(LevelDesc) * kMaxLevels + kCoarseWords * 4; }
+constexpr int kLaneSmemBytes = lane_smem_bytes(kFusedWarps);
+template <int F, bool ALT, int W>
+__global__ void __launch_bounds__(W * 32, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
                    unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
 	// dynamic shared memory (kLaneSmemBytes): [fragment-ordered weights | per-warp staging + output tiles | level table | look-ahead grid]
 	extern __shared__ __align__(16) unsigned char s_lane[];
 	uint32_t* s_w = reinterpret_cast<uint32_t*>(s_lane);
 	unsigned char (*s_warp)[kWarpSmemBytes] = reinterpret_cast<unsigned char (*)[kWarpSmemBytes]>(s_lane + kFragWords * 4);
-	LevelDesc* s_levels = reinterpret_cast<LevelDesc*>(s_lane + kFragWords * 4 + kFusedWarps * kWarpSmemBytes);
-	uint32_t* s_coarse = reinterpret_cast<uint32_t*>(s_lane + kFragWords * 4 + kFusedWarps * kWarpSmemBytes + sizeof(LevelDesc) * kMaxLevels);   // look-ahead occupancy (4 KB)
-	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += kFusedThreads) s_coarse[i] = __ldg(model.env.coarse + i);
-	for (int i = threadIdx.x; i < kFragWords / 4; i += kFusedThreads)
+	LevelDesc* s_levels = reinterpret_cast<LevelDesc*>(s_lane + kFragWords * 4 + W * kWarpSmemBytes);
+	uint32_t* s_coarse = reinterpret_cast<uint32_t*>(s_lane + kFragWords * 4 + W * kWarpSmemBytes + sizeof(LevelDesc) * kMaxLevels);   // look-ahead occupancy (4 KB)
+	if (model.env.coarse) for (int i = threadIdx.x; i < kCoarseWords; i += W * 32) s_coarse[i] = __ldg(model.env.coarse + i);
+	for (int i = threadIdx.x; i < kFragWords / 4; i += W * 32)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
 	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x, model.grid_params);
 	__syncthreads();

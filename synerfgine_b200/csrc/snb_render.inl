@@ -19,20 +19,27 @@ static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
 	return SNB_OK;
 }
 
+template <int F, bool ALT, int W>
+static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
+	static int per_sm = 0;   // per template instance
+	if (per_sm == 0) {
+		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, lane_smem_bytes(W)));
+		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT, W>, W * 32, lane_smem_bytes(W)));
+		per_sm = std::max(1, per_sm);
+	}
+	c->fused_blocks_per_sm = per_sm;
+	const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + W * 32 - 1) / (W * 32)));
+	k_nerf_march_fused<F, ALT, W><<<blocks, W * 32, lane_smem_bytes(W), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
 template <int F, bool ALT>
 static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
 	if (c->march_variant == 3) {   // default ("lane"): one ray per lane, warp-level mma.sync MLPs, 2 CTAs x 12 warps per SM
-		static int per_sm = 0;   // per template instance
-		if (per_sm == 0) {
-			SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kLaneSmemBytes));
-			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT>, kFusedThreads, kLaneSmemBytes));
-			per_sm = std::max(1, per_sm);
-		}
-		c->fused_blocks_per_sm = per_sm;
-		const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + kFusedThreads - 1) / kFusedThreads));
-		k_nerf_march_fused<F, ALT><<<blocks, kFusedThreads, kLaneSmemBytes, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
-		SNB_LAUNCHED(c);
-		return SNB_OK;
+		// CTA shape by the rays a lane will see (option "lane_warps": 0 = by tile size, else 10 | 12): results do not depend on it
+		const bool few = c->lane_warps ? c->lane_warps == kFusedWarpsFew : (size_t)n_px < (size_t)c->sm_count * SNB_LANE_CTAS * kFusedWarps * 32 * 16;
+		return few ? launch_lane<F, ALT, kFusedWarpsFew>(c, dv, out, render_mode, n_px, queue, qctl) : launch_lane<F, ALT, kFusedWarps>(c, dv, out, render_mode, n_px, queue, qctl);
 	}
 	if (c->march_variant == 5) {   // MLPs on tcgen05 tensor cores
 		static int per_sm = 0;

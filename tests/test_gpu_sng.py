@@ -180,13 +180,15 @@ def test_dead_shadow_terms_skip_is_result_identical(snb):
 
 
 @pytest.mark.parametrize("opts", [{b"sng_block": b"0", b"terms_block": b"0", b"mesh_priority": b"default", b"terms_compact": b"1"},
-                                  {b"terms_compact": b"1", b"terms_block": b"32"},
+                                  {b"terms_compact": b"1", b"terms_block": b"32", b"lane_warps": b"12"},
+                                  {b"lane_warps": b"10"},
                                   {b"sng_block": b"32", b"terms_block": b"64"},
                                   {b"sng_block": b"128", b"terms_block": b"128", b"mesh_after": b"raygen"}])
 def test_pixel_mapping_and_scheduling_options_are_result_identical(snb, opts):
     """A warp of k_raytrace / k_nerf_shadow_terms covers an 8 x 4 pixel patch (options "sng_block" / "terms_block"; "0" = 32
     pixels of a row); "terms_compact" queues the observable pixels of the shadow-term pass and runs
-    full warps over the queue; "mesh_priority" / "mesh_after" only move the mesh layer in time. Pixels are independent, so three
+    full warps over the queue; "lane_warps" forces the march's CTA shape (chosen by tile size otherwise);
+    "mesh_priority" / "mesh_after" only move the mesh layer in time. Pixels are independent, so three
     consecutive frames (later ones depend on the generator states left by earlier ones) must have the same bits as the
     defaults — on a frame whose width and height are not multiples of the patch."""
     from synerfgine_b200 import Engine, Testbed
