@@ -151,7 +151,14 @@ const char* snb_version(void);
  *   "overlap"    = "1" | "0"      mesh layer on a second stream
  *   "dead_terms" = "1" | "0"      skip NeRF shadow terms that no written pixel can observe (identical frame and RNG states)
  *   "bands"      = "1" | "2"      2: generate the lower half's rays on a side stream while the upper half is marched (identical frame; measured slower)
- * Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS / SNB_BANDS set the defaults. */
+ *   "mesh_priority" = "high" (default) | "default" | "low"   CUDA priority of the mesh layer's stream (set before the first frame)
+ *   "mesh_after" = "start" (default) | "raygen"   where the mesh layer is forked (raygen: measured slower)
+ *   "lane_warps" = "0" (default: by tile size) | "10" | "12"   CTA shape of the lane march
+ *   "sng_block"  = "128" (default) | "64" | "32" | "0"   k_raytrace threads per block, a warp = 8 x 4 pixel patch; 0 = 32 pixels of a row
+ *   "terms_block" = "0" (default) | "32" | "64" | "128"   the same for k_nerf_shadow_terms
+ *   "terms_compact" = "0" (default) | "1"   queue the observable pixels and run the shadow terms over the queue (measured slower)
+ * The six options from "mesh_priority" down leave the frames bit-identical. Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS / SNB_BANDS /
+ * SNB_MESH_PRIORITY / SNB_MESH_AFTER / SNB_LANE_WARPS / SNB_SNG_BLOCK / SNB_TERMS_BLOCK / SNB_TERMS_COMPACT set the defaults. */
 int snb_set_option(snb_ctx* ctx, const char* key, const char* value);
 
 /* ---- inputs ------------------------------------------------------------------------------------------- */
