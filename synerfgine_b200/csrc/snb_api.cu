@@ -67,7 +67,7 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		c->mesh_after_raygen = v == "raygen";
 	} else if (k == "sng_block" || k == "terms_block") {
 		const int b = atoi(v.c_str());
-		if (b != 0 && b != 32 && b != 64 && b != 128) return c->fail(SNB_ERR_ARG, "sng_block / terms_block: expected 0 | 32 | 64 | 128");
+		if ((b != 0 && b != 32 && b != 64 && b != 128 && b != 256) || (k == "sng_block" ? b > SNB_RT_THREADS : b > 128)) return c->fail(SNB_ERR_ARG, "sng_block / terms_block: expected 0 | 32 | 64 | 128");
 		(k == "sng_block" ? c->sng_block : c->terms_block) = b;
 	} else if (k == "dead_terms") {
 		c->skip_dead_terms = v != "0";
