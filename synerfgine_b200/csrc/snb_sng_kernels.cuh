@@ -270,11 +270,13 @@ SNB_D bool tile_pixel(int tiled, uint32_t n, int width, uint32_t& idx) {
 #ifndef SNB_RT_THREADS
 #define SNB_RT_THREADS 128      // largest k_raytrace block (tuning hook; option "sng_block" picks 32..SNB_RT_THREADS at run time)
 #endif
-#ifndef SNB_RT_MIN_BLOCKS
-#define SNB_RT_MIN_BLOCKS 1     // resident blocks per SM the register budget of k_raytrace is set for (tuning hook)
+#ifdef SNB_RT_MIN_BLOCKS         // resident blocks per SM the register budget of k_raytrace is set for (tuning hook; unset = ptxas' own choice, 96 registers)
+#define SNB_RT_BOUNDS __launch_bounds__(SNB_RT_THREADS, SNB_RT_MIN_BLOCKS)
+#else
+#define SNB_RT_BOUNDS __launch_bounds__(SNB_RT_THREADS)
 #endif
 // One thread per mesh-layer pixel: samples x bounces closest-hit + shading; 50/50 temporal blend into acc_rgba.
-__global__ void __launch_bounds__(SNB_RT_THREADS, SNB_RT_MIN_BLOCKS) k_raytrace(uint32_t n, const float* __restrict__ origins, const float* __restrict__ dirs, v3 up_vec, MarchEnv env,
+__global__ void SNB_RT_BOUNDS k_raytrace(uint32_t n, const float* __restrict__ origins, const float* __restrict__ dirs, v3 up_vec, MarchEnv env,
                                                   DevScene sc, RtParams rt, Rng* __restrict__ rng_states, float4* __restrict__ acc_rgba, float* __restrict__ acc_depth,
                                                   int full_w, int tx0, int ty0, int tw, int tiled) {
 	uint32_t i;
