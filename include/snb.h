@@ -145,21 +145,35 @@ void snb_destroy(snb_ctx* ctx);
 const char* snb_last_error(const snb_ctx* ctx);
 int snb_sync(snb_ctx* ctx);
 const char* snb_version(void);
-/* Implementation selectors (A/B measurements; results are identical within the parity contract):
- *   "march"      = "lane" (default: ray per lane, warp-level mma.sync) | "pool" (warp-autonomous ray pool) | "tc" (CTA tiles, tcgen05 + TMEM)
- *   "mlp"        = "mma" | "tc"   evaluator of the snb_network_inference parity tap
+/* Options. Semantics (these change what is computed; the defaults are the reference's behaviour):
+ *   "alt_schedule" = "auto" (default) | "external" | "fixed"   batch lengths of the sng compositor, see snb_get_alt_status below
+ *   "alt_batch"    = "1".."8"        batch length of alt_schedule = fixed
+ *   "alt_target_queries" = "2097152" target_n_queries of NerfTracer::trace_alt (src/testbed_nerf.cu:2188); tests lower it to exercise short batches on small frames
+ * Implementation selectors (A/B measurements; frames are bit-identical unless noted):
+ *   "mlp"        = "mma" | "tc"   evaluator of the snb_network_inference parity tap (outputs equal within fp16 rounding)
  *   "overlap"    = "1" | "0"      mesh layer on a second stream
  *   "dead_terms" = "1" | "0"      skip NeRF shadow terms that no written pixel can observe (identical frame and RNG states)
- *   "bands"      = "1" | "2"      2: generate the lower half's rays on a side stream while the upper half is marched (identical frame; measured slower)
  *   "mesh_priority" = "high" (default) | "default" | "low"   CUDA priority of the mesh layer's stream (set before the first frame)
- *   "mesh_after" = "start" (default) | "raygen"   where the mesh layer is forked (raygen: measured slower)
  *   "lane_warps" = "0" (default: by tile size) | "10" | "12"   CTA shape of the lane march
  *   "sng_block"  = "128" (default) | "64" | "32" | "0"   k_raytrace threads per block, a warp = 8 x 4 pixel patch; 0 = 32 pixels of a row
  *   "terms_block" = "0" (default) | "32" | "64" | "128"   the same for k_nerf_shadow_terms
- *   "terms_compact" = "0" (default) | "1"   queue the observable pixels and run the shadow terms over the queue (measured slower)
- * The six options from "mesh_priority" down leave the frames bit-identical. Environment SNB_MARCH / SNB_MLP / SNB_OVERLAP / SNB_DEAD_TERMS / SNB_BANDS /
- * SNB_MESH_PRIORITY / SNB_MESH_AFTER / SNB_LANE_WARPS / SNB_SNG_BLOCK / SNB_TERMS_BLOCK / SNB_TERMS_COMPACT set the defaults. */
+ * Environment SNB_<OPTION> (upper case) sets the default of an option. */
 int snb_set_option(snb_ctx* ctx, const char* key, const char* value);
+
+/* Batch schedule of the sng compositor. NerfTracer::trace_alt marches all alive rays in lock step, S_j = clamp(2^21 / n_alive_j, 1, 8)
+ * samples in iteration j (src/testbed_nerf.cu:2189-2190), and composite_kernel_nerf_alt rewinds payload.t after every iteration (:574):
+ * the last sample of a batch is composited again as the first of the next, so the image depends on S_0, S_1, ... Rays run
+ * independently here; the sequence is an input of the march and the march counts n_alive_j.
+ *   auto:     the sequence lives on the device from frame to frame; a pass whose counts contradict the sequence it used is repeated
+ *             inside the same snb_frame / snb_render_nerf_with_buffers call (at most 3 passes, conditional launches, no host sync).
+ *             Exact once `converged` is 1 (always, unless a cold start needs more than 3 passes or more than 64 batches are short).
+ *   external: one pass per call with the sequence given by snb_set_alt_schedule; the caller sums the counts (over GPUs when a frame
+ *             is tiled — n_alive_j is a whole-frame quantity) and sets the sequence they imply.
+ *   fixed:    S_j = alt_batch for all j: a deliberate deviation (= the reference for frames with <= 262144 alive rays when 8).
+ * out132: [0] passes of the last call, [1] converged, [2] first batch whose length was wrong (0xFFFFFFFF none), [3] target_n_queries,
+ * [4..67] n_alive_j of the last pass, [68..131] batch lengths the next pass will use (0 = unknown -> S_0). Synchronises. */
+int snb_get_alt_status(snb_ctx* ctx, uint32_t* out132_host);
+int snb_set_alt_schedule(snb_ctx* ctx, const uint8_t* steps_host, uint32_t n /* <= 64; later batches are 8; n = 0 forgets the sequence */);
 
 /* ---- inputs ------------------------------------------------------------------------------------------- */
 /* ≙ Testbed::load_snapshot result handed over as arrays (src/testbed.cu:4878-4992). */
@@ -206,6 +220,9 @@ int snb_march_trace(snb_ctx* ctx, const snb_view* view, uint32_t max_samples, fl
 int snb_network_inference(snb_ctx* ctx, const float* coords_dev, uint64_t n, uint16_t* out_dev, uint16_t* features_dev, uint32_t* hash_idx_dev);
 /* ≙ depth_test_world closest hit (src/synerfgine/common.cu:36-67): rays n x 6 → object id, triangle id, t. */
 int snb_trace_rays(snb_ctx* ctx, const float* rays_dev, uint32_t n, int32_t* obj_id_dev, int32_t* tri_id_dev, float* t_dev);
+/* ≙ sng::init_rand_state + curand_uniform (src/synerfgine/common.cu:22-34): XORWOW state words {v0..v4, d} of subsequences 0..n-1
+ * as the render kernels hold them, and the first n_uniform uniforms each would draw. Synchronises. */
+int snb_rng_tap(snb_ctx* ctx, uint64_t seed, uint32_t n, uint32_t n_uniform, uint32_t* states6_dev, float* uniforms_dev);
 /* Counters of the last NeRF render: [0] network samples, [1] rays launched, [2] rays that hit, [3] march batches. */
 int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
 /* Scheduling statistics of the last NeRF march (instrumentation; SURVEY.md 8d "device counters"): [0] pool iterations summed

@@ -160,8 +160,25 @@ extern "C" {
 // Per-ray schedule with a fixed batch size (see the header comment). fb (RGBA, in/out) and depth are
 // width*height; positions (alt only, may be NULL) is width*height*3 and is zero-filled first like
 // render_nerf_with_buffers does (testbed_nerf.cu:2538-2539). Returns the number of network samples.
+static uint64_t render_nerf_per_ray(const orc_model* model, const orc_view* view, int alt, int render_mode, const uint32_t* sched, uint32_t n_sched, uint32_t tail_steps,
+                                    float* fb, float* depth, float* positions, uint16_t* n_steps_out);
+
 uint64_t orc_render_nerf(const orc_model* model, const orc_view* view, int alt, int render_mode, uint32_t steps_per_batch,
                          float* fb, float* depth, float* positions, uint16_t* n_steps_out) {
+	return render_nerf_per_ray(model, view, alt, render_mode, nullptr, 0, steps_per_batch, fb, depth, positions, n_steps_out);
+}
+
+// The same per-ray loop with an explicit batch-length sequence (batch b uses sched[b], 8 past the end): what the product's march
+// evaluates once its sequence is the one the reference's lock-step loop would have produced (orc_render_nerf_wavefront's schedule_out).
+uint64_t orc_render_nerf_sched(const orc_model* model, const orc_view* view, int alt, int render_mode, const uint32_t* sched, uint32_t n_sched,
+                               float* fb, float* depth, float* positions) {
+	return render_nerf_per_ray(model, view, alt, render_mode, sched, n_sched, 8, fb, depth, positions, nullptr);
+}
+
+}
+
+static uint64_t render_nerf_per_ray(const orc_model* model, const orc_view* view, int alt, int render_mode, const uint32_t* sched, uint32_t n_sched, uint32_t steps_per_batch,
+                                    float* fb, float* depth, float* positions, uint16_t* n_steps_out) {
 	MarchEnv env = make_env(*model);
 	NetworkView net = make_network_view(*model);
 	BoundingBox train_aabb = load_aabb(model->aabb_min, model->aabb_max);
@@ -179,10 +196,13 @@ uint64_t orc_render_nerf(const orc_model* model, const orc_view* view, int alt, 
 		r.rgba = {0, 0, 0, 0}; r.depth = 0.0f;
 		advance_pos_nerf(r.p, env, view->spp, model->cone_angle_constant);
 		bool finished = !r.p.alive; // rays dead before the first iteration are compacted in iteration 1
-		for (uint32_t i = 1; r.p.alive && i < MARCH_ITER; i += S) {
-			run_batch(r, env, net, train_aabb, cam, *model, S, i, render_mode, alt != 0, &n_samples);
+		uint32_t b = 0;
+		for (uint32_t i = 1; r.p.alive && i < MARCH_ITER; ++b) {
+			const uint32_t Sb = b < n_sched ? sched[b] : S;
+			run_batch(r, env, net, train_aabb, cam, *model, Sb, i, render_mode, alt != 0, &n_samples);
 			// A ray that dies in the last possible iteration is never compacted into the hit list (:2165-2271).
-			if (!r.p.alive && i + S < MARCH_ITER) finished = true;
+			if (!r.p.alive && i + Sb < MARCH_ITER) finished = true;
+			i += Sb;
 		}
 		if (n_steps_out) n_steps_out[idx] = r.p.n_steps;
 		if (finished && r.rgba.w > 0.001f) write_hit(r, cam, render_mode, alt != 0, fb, depth, positions);
@@ -190,10 +210,13 @@ uint64_t orc_render_nerf(const orc_model* model, const orc_view* view, int alt, 
 	return n_samples;
 }
 
+extern "C" {
+
 // Replay of the reference's global wavefront schedule (trace / trace_alt, testbed_nerf.cu:2128-2401):
 // all rays advance batch by batch and S is recomputed from the global alive count.
-uint64_t orc_render_nerf_wavefront(const orc_model* model, const orc_view* view, int alt, int render_mode,
-                                   float* fb, float* depth, float* positions, uint32_t* schedule_out, uint32_t schedule_cap) {
+// target_queries = 2 * 1024 * 1024 in the reference (:2188); alive_out (may be NULL) receives n_alive of every iteration.
+uint64_t orc_render_nerf_wavefront(const orc_model* model, const orc_view* view, int alt, int render_mode, uint32_t target_queries,
+                                   float* fb, float* depth, float* positions, uint32_t* schedule_out, uint32_t* alive_out, uint32_t schedule_cap) {
 	MarchEnv env = make_env(*model);
 	NetworkView net = make_network_view(*model);
 	BoundingBox train_aabb = load_aabb(model->aabb_min, model->aabb_max);
@@ -224,8 +247,9 @@ uint64_t orc_render_nerf_wavefront(const orc_model* model, const orc_view* view,
 		alive.swap(next);
 		uint32_t n_alive = (uint32_t)alive.size();
 		if (n_alive == 0) break;
-		uint32_t S = std::min(std::max((2u * 1024 * 1024) / n_alive, 1u), 8u);
+		uint32_t S = std::min(std::max(target_queries / n_alive, 1u), 8u);
 		if (schedule_out && it < schedule_cap) schedule_out[it] = S;
+		if (alive_out && it < schedule_cap) alive_out[it] = n_alive;
 		++it;
 		for (uint32_t k : alive) run_batch(rays[k], env, net, train_aabb, cam, *model, S, i, render_mode, alt != 0, &n_samples);
 		i += S;

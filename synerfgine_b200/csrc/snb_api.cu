@@ -9,6 +9,8 @@
 #include <cmath>
 #include <algorithm>
 #include <cstdio>
+#include <cctype>
+#include <string>
 #include <vector>
 #include "snb_context.cuh"
 
@@ -43,10 +45,21 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 	if (!c || !key || !value) return SNB_ERR_ARG;
 	const std::string k(key), v(value);
 	if (k == "march") {
-		if (v == "v3" || v == "lane") c->march_variant = 3;
-		else if (v == "v4" || v == "pool") c->march_variant = 4;
-		else if (v == "tc") c->march_variant = 5;
-		else return c->fail(SNB_ERR_ARG, "march: expected lane | pool | tc");
+		if (v == "lane") c->march_variant = 3;
+		else return c->fail(SNB_ERR_ARG, "march: expected lane");
+	} else if (k == "alt_schedule") {
+		if (v == "auto") c->alt_mode = 0;
+		else if (v == "external") c->alt_mode = 1;
+		else if (v == "fixed") c->alt_mode = 2;
+		else return c->fail(SNB_ERR_ARG, "alt_schedule: expected auto | external | fixed");
+	} else if (k == "alt_batch") {
+		const int b = atoi(v.c_str());
+		if (b < 1 || b > 8) return c->fail(SNB_ERR_ARG, "alt_batch: expected 1..8");
+		c->alt_batch = b;
+	} else if (k == "alt_target_queries") {
+		const long long t = atoll(v.c_str());
+		if (t < 1 || t > 0x7FFFFFFFll) return c->fail(SNB_ERR_ARG, "alt_target_queries: expected a positive 31-bit count");
+		c->alt_target_queries = (uint32_t)t;
 	} else if (k == "mlp") {
 		if (v == "mma") c->mlp_variant = 0;
 		else if (v == "tc") c->mlp_variant = 1;
@@ -55,16 +68,10 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		c->overlap_layers = v != "0";
 	} else if (k == "mesh_priority") {
 		c->mesh_priority = v == "high" ? 1 : v == "low" ? -1 : 0;
-	} else if (k == "bands") {
-		c->bands = v == "2" ? 2 : 1;
 	} else if (k == "lane_warps") {
 		const int w = atoi(v.c_str());
 		if (w != 0 && w != kFusedWarpsFew && w != kFusedWarps) return c->fail(SNB_ERR_ARG, "lane_warps: expected 0 | 10 | 12");
 		c->lane_warps = w;
-	} else if (k == "terms_compact") {
-		c->terms_compact = v != "0";
-	} else if (k == "mesh_after") {
-		c->mesh_after_raygen = v == "raygen";
 	} else if (k == "sng_block" || k == "terms_block") {
 		const int b = atoi(v.c_str());
 		if ((b != 0 && b != 32 && b != 64 && b != 128 && b != 256) || (k == "sng_block" ? b > SNB_RT_THREADS : b > 128)) return c->fail(SNB_ERR_ARG, "sng_block / terms_block: expected 0 | 32 | 64 | 128");
@@ -90,23 +97,18 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	snb_ctx* c = new snb_ctx();
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
-	if (const char* mv = getenv("SNB_MARCH")) snb_set_option(c, "march", mv);
-	if (const char* mv = getenv("SNB_MLP")) snb_set_option(c, "mlp", mv);
-	if (const char* mv = getenv("SNB_OVERLAP")) snb_set_option(c, "overlap", mv);
-	if (const char* mv = getenv("SNB_DEAD_TERMS")) snb_set_option(c, "dead_terms", mv);
-	if (const char* mv = getenv("SNB_LANE_WARPS")) snb_set_option(c, "lane_warps", mv);
-	if (const char* mv = getenv("SNB_TERMS_COMPACT")) snb_set_option(c, "terms_compact", mv);
-	if (const char* mv = getenv("SNB_MESH_AFTER")) snb_set_option(c, "mesh_after", mv);
-	if (const char* mv = getenv("SNB_SNG_BLOCK")) snb_set_option(c, "sng_block", mv);
-	if (const char* mv = getenv("SNB_TERMS_BLOCK")) snb_set_option(c, "terms_block", mv);
-	if (const char* mv = getenv("SNB_BANDS")) snb_set_option(c, "bands", mv);
-	if (const char* mv = getenv("SNB_MESH_PRIORITY")) snb_set_option(c, "mesh_priority", mv);
-	if (cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_band0, cudaEventDisableTiming) != cudaSuccess ||
-	    cudaEventCreateWithFlags(&c->ev_band1, cudaEventDisableTiming) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
+	// SNB_<OPTION> in the environment sets the default of snb_set_option(ctx, "<option>", ...) (A/B runs without touching the caller)
+	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch"};
+	for (const char* opt : kEnvOptions) {
+		std::string env = std::string("SNB_") + opt;
+		for (char& ch : env) ch = (char)toupper((unsigned char)ch);
+		if (const char* mv = getenv(env.c_str())) snb_set_option(c, opt, mv);
+	}
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
-	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
+	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess || c->d_alt.reserve(sizeof(AltState)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
 	cudaMemsetAsync(c->d_counters.p, 0, sizeof(NerfCounters), c->stream);
+	cudaMemsetAsync(c->d_alt.p, 0, sizeof(AltState), c->stream);
 	memset(&c->model, 0, sizeof c->model);
 	*out = c;
 	return SNB_OK;
@@ -117,11 +119,10 @@ void snb_destroy(snb_ctx* c) {
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
 	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_present, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
-	                  &c->d_counters, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
+	                  &c->d_counters, &c->d_alt, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
 	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth};
 	for (DevBuf* b : bufs) b->release();
 	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
-	if (c->stream3) { cudaStreamSynchronize(c->stream3); cudaStreamDestroy(c->stream3); cudaEventDestroy(c->ev_band0); cudaEventDestroy(c->ev_band1); }
 	if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;

@@ -11,9 +11,7 @@
 #include "../../include/snb.h"
 #include "snb_device.cuh"
 #include "snb_nerf_kernels.cuh"
-#include "snb_pool_kernel.cuh"
 #include "snb_mlp_tc.cuh"
-#include "snb_march_tc_kernel.cuh"
 #include "snb_present.cuh"
 #include "snb_sng_kernels.cuh"
 
@@ -66,10 +64,17 @@ struct snb_ctx {
 	snb::DevBuf d_syn_origins, d_syn_dirs, d_syn_rgba, d_syn_depth;
 	bool syn_reset = true;
 	int syn_w = 0, syn_h = 0;
-	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_terms_list, d_out_rgba, d_out_depth;
+	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
+	int lane_blocks_per_sm[16] = {};   // resident CTAs per SM of each k_nerf_march_fused instance launched by THIS context (0 = not set up yet)
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
-	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused), 4 = ray pool (snb_pool_kernel.cuh), 5 = tcgen05 MLPs (snb_march_tc_kernel.cuh)
+	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused)
+	// batch schedule of the sng compositor (AltState in snb_nerf_kernels.cuh): 0 = "auto" (device-resident sequence, verified and
+	// repeated inside the frame), 1 = "external" (one pass; the caller reads the counts and sets the sequence: multi-GPU), 2 = "fixed"
+	int alt_mode = 0;
+	int alt_batch = 8;                 // batch length of alt_mode 2
+	uint32_t alt_target_queries = 2u * 1024u * 1024u;   // target_n_queries of trace_alt (src/testbed_nerf.cu:2188)
+	snb::DevBuf d_alt;
 
 	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)
 	static const int kStages = 5;   // 0 nerf raygen, 1 nerf fused march, 2 nerf normals+shadows, 3 mesh layer, 4 overlay
@@ -80,18 +85,13 @@ struct snb_ctx {
 
 	// second stream for the mesh layer of snb_frame: it does not depend on the NeRF layer until the overlay, and both are
 	// latency-bound, so they run concurrently (the reference serialises them with host syncs, engine.cu:386-406)
-	cudaStream_t stream2 = nullptr, stream3 = nullptr;   // mesh layer; lower band's ray generation
-	cudaEvent_t ev_band0 = nullptr, ev_band1 = nullptr;
-	int bands = 1;                                          // option "bands": 2 was measured slower (7.18 vs 6.97 ms), kept for A/B
+	cudaStream_t stream2 = nullptr;   // mesh layer
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool overlap_layers = true;
 	int mesh_priority = 1;         // stream priority of the mesh layer's stream: +1 high (default: the mesh layer finishes under ray generation and the march runs undisturbed), 0 default, -1 low (option "mesh_priority")
-	bool mesh_after_raygen = false;   // fork the mesh layer behind NeRF ray generation instead of at frame start (option "mesh_after" = "raygen")
-	const void* deferred_syn_view = nullptr; const snb_rt_params* deferred_syn_rt = nullptr;   // set by snb_frame for the duration of one render_nerf_layer call
 	int lane_warps = 0;            // lane march CTA shape: 0 = chosen by tile size, 10 | 12 = forced (option "lane_warps")
 	int sng_block = 128;           // k_raytrace: threads per block with a warp = 8 x 4 pixels; 0 = row-linear mapping (option "sng_block")
 	int terms_block = 0;           // k_nerf_shadow_terms: same choice (option "terms_block"); row-linear measured faster there
-	bool terms_compact = false;    // observable pixels queued by k_nerf_shadow_classify, k_nerf_shadow_terms over the queue with full warps (option "terms_compact"); measured slower on C2 (post 0.65 against 0.60 ms: the divergence is inside the BVH / DDA work, not in who does it), so off
 	bool skip_dead_terms = true;   // k_nerf_shadow_terms: skip terms no written pixel can observe (option "dead_terms")
 
 	int fail(int code, const std::string& msg) { err = msg; return code; }

@@ -35,6 +35,69 @@ struct NerfOut {                     // tile-sized output buffers
 	float* positions;                // xyz per pixel (alt path) or nullptr
 };
 
+// ---- batch schedule of the sng compositor ------------------------------------------------------------------------------------
+// NerfTracer::trace_alt marches all alive rays in lock step, S = clamp(2^21 / n_alive, 1, 8) samples per iteration
+// (src/testbed_nerf.cu:2189-2190), and composite_kernel_nerf_alt rewinds payload.t to the last composited sample after every
+// iteration (:574), so the last sample of a batch is evaluated again as the first sample of the next: the image depends on
+// the sequence S_0, S_1, ... Here rays run independently, so the sequence is an INPUT (kAltSched entries, 8 afterwards; entry 0
+// is always derived from the queued-ray count, which is exact) and the kernel counts the rays that start each batch; k_alt_verify
+// derives the sequence those counts imply and flags a mismatch, in which case the march is repeated with the corrected sequence
+// (conditional launches, no host round trip). n_alive_j depends only on S_0..S_{j-1}, so every pass fixes at least one more
+// entry; from one frame to the next the sequence rarely changes and one pass suffices.
+constexpr int kAltSched = 64;
+struct AltState {                     // device-resident, one per context
+	uint32_t hist[kAltSched];         // rays that started batch j in the last pass (n_alive_j of the reference)
+	uint8_t sched[kAltSched];         // batch lengths used by the next pass; 0 = not known yet (use S_0)
+	uint32_t redo;                    // set by k_alt_verify: the pass just made used a sequence its own counts contradict
+	uint32_t passes, converged, last_mismatch;
+};
+struct AltCtl {
+	AltState* st;                     // nullptr: stock path / fixed batch length
+	uint32_t target_queries;          // 2 * 1024 * 1024 in the reference
+	uint32_t fixed_steps;             // != 0: constant batch length (option alt_batch), no counting
+	uint32_t conditional;             // run only if st->redo is set (second and third pass)
+	uint32_t external;                // the caller owns the sequence (a tile of a larger frame): entry 0 is taken from it too
+};
+SNB_HD uint32_t alt_steps_for(uint32_t target, uint32_t n_alive) {
+	uint32_t s = n_alive ? target / n_alive : 8u;
+	return s < 1u ? 1u : (s > 8u ? 8u : s);
+}
+__global__ void k_alt_verify(AltState* st, uint32_t target, const unsigned int* __restrict__ queue_tail, uint32_t last_pass, uint32_t external) {
+	__shared__ uint32_t s_bad;
+	const int j = threadIdx.x;
+	if (j == 0) s_bad = 0xFFFFFFFFu;
+	__syncthreads();
+	if (st->passes != 0 && !st->redo) return;         // a conditional pass that did not run: nothing new to verify (uniform)
+	const uint32_t n = st->hist[j];
+	uint32_t used = st->sched[j];
+	if ((j == 0 && !external) || used == 0) used = alt_steps_for(target, *queue_tail);
+	const uint32_t want = n ? alt_steps_for(target, n) : 8u;
+	if (n && want != used) atomicMin(&s_bad, (uint32_t)j);
+	if (j == kAltSched - 1 && n > target / 8u) atomicMin(&s_bad, (uint32_t)kAltSched);   // still below 8 after the last tracked batch: inexact beyond
+	__syncthreads();
+	if (!external) st->sched[j] = (uint8_t)want;   // external: the counts of one tile say nothing about the frame; the caller sums them
+	if (j == 0) {
+		const bool ok = s_bad == 0xFFFFFFFFu;
+		st->passes += 1; st->converged = ok ? 1u : 0u; st->last_mismatch = s_bad;
+		st->redo = (!ok && !last_pass && s_bad < (uint32_t)kAltSched) ? 1u : 0u;
+	}
+}
+// Start of a march pass: the first pass always runs and resets the per-frame state; later passes run only after a mismatch and
+// first undo what the previous pass wrote (tile buffers are cleared like ray generation clears them).
+__global__ void __launch_bounds__(256) k_alt_begin_pass(AltState* st, uint32_t first_pass, NerfOut out, uint32_t n_px, unsigned int* __restrict__ queue_head,
+                                                        NerfCounters* __restrict__ counters) {
+	if (!first_pass && !st->redo) return;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i == 0) { *queue_head = 0u; if (first_pass) { st->passes = 0; st->redo = 0; st->converged = 0; } if (counters) { counters->samples = 0; counters->rays = 0; counters->hits = 0; } }
+	if (i < (uint32_t)kAltSched) st->hist[i] = 0u;
+	if (first_pass) return;
+	for (uint32_t p = i; p < n_px; p += gridDim.x * blockDim.x) {
+		out.fb[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+		out.depth[p] = kMaxDepth;
+		if (out.positions) { out.positions[p * 3 + 0] = 0.0f; out.positions[p * 3 + 1] = 0.0f; out.positions[p * 3 + 2] = 0.0f; }
+	}
+}
+
 SNB_D float act_logistic(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 SNB_D float act_rgb(float v, int act) {
 	switch (act) {
@@ -198,7 +261,8 @@ constexpr int kLaneSmemBytes = lane_smem_bytes(kFusedWarps);
 template <int F, bool ALT, int W>
 __global__ void __launch_bounds__(W * 32, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
-                   unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
+                   unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters, AltCtl alt) {
+	if (alt.conditional && !alt.st->redo) return;   // second / third pass of the batch-schedule iteration: only after a mismatch (uniform)
 	// dynamic shared memory (kLaneSmemBytes): [fragment-ordered weights | per-warp staging + output tiles | level table | look-ahead grid]
 	extern __shared__ __align__(16) unsigned char s_lane[];
 	uint32_t* s_w = reinterpret_cast<uint32_t*>(s_lane);
@@ -209,12 +273,27 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	for (int i = threadIdx.x; i < kFragWords / 4; i += W * 32)
 		reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(model.mlp_frag) + i);
 	if (threadIdx.x < kFeat / F) s_levels[threadIdx.x] = make_level_desc(model.grid, threadIdx.x, model.grid_params);
+	// batch schedule of the sng compositor (see AltState): lengths of batches 0..kAltSched-1 (8 afterwards) and this CTA's share of the counts
+	__shared__ uint8_t s_sched[kAltSched];
+	__shared__ uint32_t s_hist[kAltSched];
+	const unsigned int n_rays = *queue_tail;
+	if (threadIdx.x < kAltSched) {
+		uint32_t steps = kBatchSteps;
+		if (ALT && alt.fixed_steps) steps = alt.fixed_steps;
+		else if (ALT && alt.st) {
+			const uint32_t s0 = alt_steps_for(alt.target_queries, n_rays);
+			steps = (threadIdx.x == 0 && !alt.external) ? s0 : alt.st->sched[threadIdx.x];
+			if (steps == 0) steps = s0;
+		}
+		s_sched[threadIdx.x] = (uint8_t)steps;
+		s_hist[threadIdx.x] = 0u;
+	}
 	__syncthreads();
+	const bool count_batches = ALT && alt.st && !alt.fixed_steps;
 
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	__half* tile = reinterpret_cast<__half*>(s_warp[warp]);
 	__half* out_tile = reinterpret_cast<__half*>(s_warp[warp] + kWarpTileBytes);
-	const unsigned int n_rays = *queue_tail;
 	MarchEnv env = model.env;
 	if (env.coarse) env.coarse = s_coarse;
 	const v3 cam_fwd = view.cam.c2;
@@ -226,6 +305,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	float4 rgba = make_float4(0, 0, 0, 0);
 	uint32_t idx = 0, step_i = 1;
 	int k = 0, n_empty = 0;
+	uint32_t batch = 0, batch_steps = s_sched[0];   // index and length of the ray's current batch
 	bool alive = false, drained = false;
 	float max_weight = 0.0f;
 	{ // zero the whole row once so never-filled rows hold finite values
@@ -237,7 +317,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 
 	auto finish = [&]() {
 		alive = false;
-		if (step_i + kBatchSteps >= kMarchIter) return;   // died in the last possible iteration: never compacted into the hit list
+		if (step_i + batch_steps >= kMarchIter) return;   // died in the last possible iteration: never compacted into the hit list
 		if (ALT) t = depth / dot(cam_fwd, d);             // payload.t rewrite at the end of composite_kernel_nerf_alt
 		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth); ++n_hits; }
 	};
@@ -258,6 +338,8 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				o = mk3(q0.x, q0.y, q0.z); t = q0.w; d = mk3(q1.x, q1.y, q1.z); idx = __float_as_uint(q1.w);
 				idir = 1.0f / d;
 				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; n_empty = 0; alive = true;
+				batch = 0; batch_steps = s_sched[0];
+				if (count_batches) atomicAdd(&s_hist[0], 1u);
 				++n_launched;
 				// SH block of the staged row (k-tile 2): encoded by ray generation, copied as is
 				const uint4 s0 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 2), s1 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 3);
@@ -333,12 +415,17 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				const float inv_a = 1.0f / rgba.w;
 				rgba.x *= inv_a; rgba.y *= inv_a; rgba.z *= inv_a; rgba.w *= inv_a;
 				fin = true;
-			} else if (++k == kBatchSteps) {
+			} else if (++k == (int)batch_steps) {
 				// batch boundary: the sng compositor rewinds t to the last composited sample
 				if (ALT) t = depth / dot(cam_fwd, d);
 				k = 0;
-				step_i += kBatchSteps;
+				step_i += batch_steps;
 				if (step_i >= kMarchIter) alive = false;         // iteration budget exhausted: ray is dropped, not written
+				else {
+					++batch;
+					if (batch < (uint32_t)kAltSched) { batch_steps = s_sched[batch]; if (count_batches) atomicAdd(&s_hist[batch], 1u); }
+					else batch_steps = ALT && alt.fixed_steps ? alt.fixed_steps : kBatchSteps;
+				}
 			}
 		}
 	}
@@ -354,6 +441,10 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		atomicAdd(&counters->samples, (unsigned long long)n_samples);
 		atomicAdd(&counters->hits, (unsigned long long)n_hits);
 		atomicAdd(&counters->rays, (unsigned long long)n_launched);
+	}
+	if (count_batches) {
+		__syncthreads();
+		if (threadIdx.x < kAltSched && s_hist[threadIdx.x]) atomicAdd(&alt.st->hist[threadIdx.x], s_hist[threadIdx.x]);
 	}
 }
 

@@ -19,9 +19,12 @@ static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
 	return SNB_OK;
 }
 
+// Per-context, per-kernel-variant launch set-up (the dynamic shared-memory opt-in is a per-device attribute and a context belongs to
+// one device; nothing process-wide is cached).
 template <int F, bool ALT, int W>
-static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
-	static int per_sm = 0;   // per template instance
+static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
+	const int slot = (F == 1 ? 0 : F == 2 ? 1 : F == 4 ? 2 : 3) * 4 + (ALT ? 2 : 0) + (W == kFusedWarps ? 1 : 0);
+	int& per_sm = c->lane_blocks_per_sm[slot];
 	if (per_sm == 0) {
 		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, lane_smem_bytes(W)));
 		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT, W>, W * 32, lane_smem_bytes(W)));
@@ -29,66 +32,34 @@ static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int re
 	}
 	c->fused_blocks_per_sm = per_sm;
 	const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + W * 32 - 1) / (W * 32)));
-	k_nerf_march_fused<F, ALT, W><<<blocks, W * 32, lane_smem_bytes(W), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+	k_nerf_march_fused<F, ALT, W><<<blocks, W * 32, lane_smem_bytes(W), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt);
 	SNB_LAUNCHED(c);
 	return SNB_OK;
 }
 
 template <int F, bool ALT>
-static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
-	if (c->march_variant == 3) {   // default ("lane"): one ray per lane, warp-level mma.sync MLPs, 2 CTAs x 12 warps per SM
-		// CTA shape by the rays a lane will see (option "lane_warps": 0 = by tile size, else 10 | 12): results do not depend on it
-		const bool few = c->lane_warps ? c->lane_warps == kFusedWarpsFew : (size_t)n_px < (size_t)c->sm_count * SNB_LANE_CTAS * kFusedWarps * 32 * 16;
-		return few ? launch_lane<F, ALT, kFusedWarpsFew>(c, dv, out, render_mode, n_px, queue, qctl) : launch_lane<F, ALT, kFusedWarps>(c, dv, out, render_mode, n_px, queue, qctl);
-	}
-	if (c->march_variant == 5) {   // MLPs on tcgen05 tensor cores
-		static int per_sm = 0;
-		if (per_sm == 0) {
-			SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_tc<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
-			SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_tc<F, ALT>, tc::kTileRows, kTcSmemBytes));
-			// registers (96) and shared memory (39 KB) allow 5 CTAs / SM (ncu launch__occupancy_limit_*); the occupancy query
-			// answered < 2 for this kernel on driver 580.159, so fall back to the limits known from the build. TMEM: 512 columns / SM.
-			if (per_sm < 2) per_sm = 5;
-			per_sm = std::max(1, std::min(per_sm, (int)(512 / tc::kTmemColsCompact)));
-		}
-		c->fused_blocks_per_sm = per_sm;
-		const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + tc::kTileRows - 1) / tc::kTileRows));
-		k_nerf_march_tc<F, ALT><<<blocks, tc::kTileRows, kTcSmemBytes, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
-		SNB_LAUNCHED(c);
-		return SNB_OK;
-	}
-	static int per_sm = 0;
-	if (per_sm == 0) {
-		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_pool<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PoolSmem)));
-		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_pool<F, ALT>, kPoolThreads, sizeof(PoolSmem)));
-		per_sm = std::max(1, per_sm);
-	}
-	c->fused_blocks_per_sm = per_sm;
-	const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + kPoolSlots - 1) / kPoolSlots));
-	k_nerf_march_pool<F, ALT><<<blocks, kPoolThreads, sizeof(PoolSmem), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
-	SNB_LAUNCHED(c);
-	return SNB_OK;
+static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
+	// CTA shape by the rays a lane will see (option "lane_warps": 0 = by tile size, else 10 | 12): results do not depend on it
+	const bool few = c->lane_warps ? c->lane_warps == kFusedWarpsFew : (size_t)n_px < (size_t)c->sm_count * SNB_LANE_CTAS * kFusedWarps * 32 * 16;
+	return few ? launch_lane<F, ALT, kFusedWarpsFew>(c, dv, out, render_mode, n_px, queue, qctl, alt) : launch_lane<F, ALT, kFusedWarps>(c, dv, out, render_mode, n_px, queue, qctl, alt);
 }
 
 template <bool ALT>
-static int launch_fused_f(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl) {
+static int launch_fused_f(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
 	switch (c->feat_per_level) {
-		case 1: return launch_fused<1, ALT>(c, dv, out, render_mode, n_px, queue, qctl);
-		case 2: return launch_fused<2, ALT>(c, dv, out, render_mode, n_px, queue, qctl);
-		case 4: return launch_fused<4, ALT>(c, dv, out, render_mode, n_px, queue, qctl);
-		default: return launch_fused<8, ALT>(c, dv, out, render_mode, n_px, queue, qctl);
+		case 1: return launch_fused<1, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
+		case 2: return launch_fused<2, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
+		case 4: return launch_fused<4, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
+		default: return launch_fused<8, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
 	}
 }
 
 // NeRF layer into tile-sized buffers. alt = sng compositor (trace_alt) + positions.
 //
-// Two bands (option "bands" = "2", tiles of >= 256 rows): ray generation is issue-bound (89 % issue active) and the march is
-// latency-bound (51 %), so the lower band's rays can be generated on a side stream WHILE the upper band is marched; each band
-// has its own queue segment and head / tail counters, both write the same tile buffers, and the per-pixel results do not
-// depend on the split (rays are independent; normals and shadows run afterwards on the whole tile). Measured on C2: 7.18 ms
-// per frame against 6.97 ms with one band — two half-sized persistent marches lose more in ramp-up and tail than the
-// overlap wins — so the default is one band; the option stays for A/B runs.
-static int render_syn_layer(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, cudaStream_t st);
+// sng path: the batch lengths of the reference's lock-step march (AltState, snb_nerf_kernels.cuh) are carried on the device from
+// frame to frame; a pass whose own ray counts contradict the lengths it used is repeated (at most kAltPasses passes, each later
+// one a conditional launch that returns at once when the previous pass verified) — all enqueued without a host round trip.
+static const int kAltPasses = 3;
 static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render_mode, float* fb, float* depth, float* positions) {
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	const int n_px = dv.tw * dv.th;
@@ -99,34 +70,29 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches_x = (dv.tw + 7) / 8, patches_y = (dv.th + 3) / 4;
 	const int patches = patches_x * patches_y;
-	const bool two = c->bands == 2 && dv.th >= 256 && c->stream3;
-	const int split = two ? (patches_y / 2) * patches_x : patches;           // first patch of the lower band
 	RayRec* q0 = c->d_queue.as<RayRec>();
-	RayRec* q1 = q0 + (size_t)split * 32;                                   // a band never queues more rays than it has pixels
 	c->stage_begin(0);
-	k_nerf_raygen<<<(split + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, split);
+	k_nerf_raygen<<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, patches);
 	SNB_LAUNCHED(c);
 	c->stage_end(0);
-	if (c->deferred_syn_view) {   // option "mesh_after" = "raygen": the mesh layer is forked here, behind ray generation
-		const DevView* sv = static_cast<const DevView*>(c->deferred_syn_view); c->deferred_syn_view = nullptr;
-		SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-		SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
-		const int rc2 = render_syn_layer(c, *sv, c->deferred_syn_rt, c->stream2); if (rc2) return rc2;
-		SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
-	}
-	if (two) {
-		SNB_CUDA(c, cudaEventRecord(c->ev_band0, c->stream));
-		SNB_CUDA(c, cudaStreamWaitEvent(c->stream3, c->ev_band0, 0));
-		k_nerf_raygen<<<(patches - split + 3) / 4, 128, 0, c->stream3>>>(dv, c->model.env, out, q1, qctl + 2, split, patches);
-		SNB_LAUNCHED(c);
-		SNB_CUDA(c, cudaEventRecord(c->ev_band1, c->stream3));
-	}
 	c->stage_begin(1);
-	int rc = alt ? launch_fused_f<true>(c, dv, out, render_mode, split * 32, q0, qctl) : launch_fused_f<false>(c, dv, out, render_mode, split * 32, q0, qctl);
-	if (rc == SNB_OK && two) {
-		SNB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_band1, 0));
-		rc = alt ? launch_fused_f<true>(c, dv, out, render_mode, (patches - split) * 32, q1, qctl + 2)
-		         : launch_fused_f<false>(c, dv, out, render_mode, (patches - split) * 32, q1, qctl + 2);
+	int rc = SNB_OK;
+	AltCtl ctl; ctl.st = nullptr; ctl.target_queries = c->alt_target_queries; ctl.fixed_steps = 0; ctl.conditional = 0; ctl.external = c->alt_mode == 1;
+	if (!alt) rc = launch_fused_f<false>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl);
+	else if (c->alt_mode == 2) { ctl.fixed_steps = (uint32_t)c->alt_batch; rc = launch_fused_f<true>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl); }
+	else {
+		AltState* st = c->d_alt.as<AltState>();
+		ctl.st = st;
+		const int passes = c->alt_mode == 1 ? 1 : kAltPasses;   // "external": the caller owns the sequence (multi-GPU: counts are summed over ranks)
+		for (int pass = 0; pass < passes && rc == SNB_OK; ++pass) {
+			k_alt_begin_pass<<<pass == 0 ? 1 : std::min(2 * c->sm_count, (n_px + 255) / 256), 256, 0, c->stream>>>(st, pass == 0, out, (uint32_t)n_px, qctl + 1, c->d_counters.as<NerfCounters>());
+			SNB_LAUNCHED(c);
+			ctl.conditional = pass > 0;
+			rc = launch_fused_f<true>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl);
+			if (rc != SNB_OK) break;
+			k_alt_verify<<<1, kAltSched, 0, c->stream>>>(st, c->alt_target_queries, qctl, (pass == passes - 1 || c->alt_mode == 1) ? 1u : 0u, c->alt_mode == 1 ? 1u : 0u);
+			SNB_LAUNCHED(c);
+		}
 	}
 	c->stage_end(1);
 	return rc;
@@ -201,20 +167,9 @@ static int nerf_post(snb_ctx* c, const DevView& dv, const snb_rt_params* rt, int
 		const int sb = c->terms_block;
 		const dim3 grid_px = sb ? dim3(((dv.tw + 7) / 8 + sb / 32 - 1) / (sb / 32), (dv.th + 3) / 4) : dim3((n + 127) / 128);
 		const float4* layer = (render_mode != 8 && c->skip_dead_terms) ? reinterpret_cast<const float4*>(fb) : nullptr;
-		const uint32_t* list = nullptr; uint32_t* list_count = nullptr;
-		if (layer && c->terms_compact) {
-			SNB_CUDA(c, c->d_terms_list.reserve((size_t)n * 4));
-			list_count = c->d_qctl.as<unsigned int>() + 8;
-			SNB_CUDA(c, cudaMemsetAsync(list_count, 0, 4, c->stream));
-			k_nerf_shadow_classify<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->scene, c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(), layer, dv.tw, dv.th,
-			                                                              rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0, c->d_terms_list.as<uint32_t>(), list_count);
-			SNB_LAUNCHED(c);
-			list = c->d_terms_list.as<uint32_t>(); layer = nullptr;
-		}
-		k_nerf_shadow_terms<<<list ? dim3((n + 127) / 128) : grid_px, (sb && !list) ? sb : 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
-		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(),
-		                                                            layer, dv.tw, dv.th,
-		                                                            rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0, sb, list, list_count);
+		k_nerf_shadow_terms<<<grid_px, sb ? sb : 128, 0, c->stream>>>(n, positions, normals, env, c->scene, rt->nerf_shadow_intensity, rt->nerf_on_nerf_shadow_threshold,
+		                                                            c->d_rng_nerf.as<Rng>(), c->d_terms.as<float>(), layer, dv.tw, dv.th,
+		                                                            rt->nerf_shadow_kernel / 2, dv.width, dv.tx0, dv.ty0, sb);
 		SNB_LAUNCHED(c);
 		k_nerf_shadow_apply<<<grid2, 128, 0, c->stream>>>(dv.tw, dv.th, rt->nerf_shadow_kernel / 2, rt->nerf_shadow_intensity, render_mode, c->d_terms.as<float>(),
 		                                                  reinterpret_cast<float4*>(fb), nullptr);
@@ -321,16 +276,12 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 			SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
 		}
 	}
-	const bool defer = fork && c->mesh_after_raygen;
-	if (defer) { c->deferred_syn_view = &syn; c->deferred_syn_rt = rt; }
-	else {
-		if (fork) {
-			SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-			SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
-		}
-		rc = render_syn_layer(c, syn, rt, fork ? c->stream2 : c->stream); if (rc) return rc;
-		if (fork) SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+	if (fork) {
+		SNB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+		SNB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
 	}
+	rc = render_syn_layer(c, syn, rt, fork ? c->stream2 : c->stream); if (rc) return rc;
+	if (fork) SNB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
 	// 2. NeRF layer with mesh shadows (Testbed::render sng overload)
 	SNB_CUDA(c, c->d_nerf_fb.reserve(n_nerf * 16));
 	SNB_CUDA(c, c->d_nerf_depth.reserve(n_nerf * 4));
@@ -338,7 +289,6 @@ int snb_frame(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_
 		SNB_CUDA(c, c->d_positions.reserve(n_nerf * 12));
 		SNB_CUDA(c, c->d_normals.reserve(n_nerf * 12));
 		rc = render_nerf_layer(c, nerf, true, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_nerf_depth.as<float>(), c->d_positions.as<float>());
-		c->deferred_syn_view = nullptr;
 		if (rc) return rc;
 		rc = nerf_post(c, nerf, rt, SNB_MODE_SHADE, c->d_nerf_fb.as<float>(), c->d_positions.as<float>(), c->d_normals.as<float>()); if (rc) return rc;
 	}

@@ -351,14 +351,9 @@ __global__ void SNB_RT_BOUNDS k_raytrace(uint32_t n, const float* __restrict__ o
 // generator states — and with them every later frame — stay identical. Not used in ShadowDepth mode (which shows the mean itself).
 __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const float* __restrict__ positions, const float* __restrict__ normals, MarchEnv env, DevScene sc,
                                                           float intensity, float thr, Rng* __restrict__ rng_states, float* __restrict__ terms,
-                                                          const float4* __restrict__ layer, int width, int height, int half_k, int full_w, int tx0, int ty0, int tiled,
-                                                          const uint32_t* __restrict__ list, const uint32_t* __restrict__ list_count) {
+                                                          const float4* __restrict__ layer, int width, int height, int half_k, int full_w, int tx0, int ty0, int tiled) {
 	uint32_t q;
-	if (list) {   // compacted: thread t takes the t-th pixel k_nerf_shadow_classify queued (all of them observable)
-		const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-		if (t >= *list_count) return;
-		q = list[t];
-	} else if (!tile_pixel(tiled, n, width, q)) return;
+	if (!tile_pixel(tiled, n, width, q)) return;
 	const size_t gq = (size_t)(ty0 + (int)(q / (uint32_t)width)) * full_w + tx0 + (int)(q % (uint32_t)width);   // generator states are per GLOBAL pixel
 	Rng rng = rng_states[gq];
 	bool observable = true;
@@ -400,42 +395,6 @@ __global__ void __launch_bounds__(128) k_nerf_shadow_terms(uint32_t n, const flo
 		}
 	}
 	terms[q] = overall;
-	rng_states[gq] = rng;
-}
-
-// Pass 1a of the compacted form (option "terms_compact"): the observable test of k_nerf_shadow_terms for every pixel. A pixel
-// no written pixel can observe is finished here exactly as there (term 1, the generator draws what light_sample would have
-// drawn); the others are queued, and k_nerf_shadow_terms then runs over the queue with full warps. The queue order is
-// whatever the atomics give; every term depends on its own pixel only, so the results do not.
-__global__ void __launch_bounds__(128) k_nerf_shadow_classify(uint32_t n, DevScene sc, Rng* __restrict__ rng_states, float* __restrict__ terms,
-                                                             const float4* __restrict__ layer, int width, int height, int half_k, int full_w, int tx0, int ty0,
-                                                             uint32_t* __restrict__ list, uint32_t* __restrict__ list_count) {
-	const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-	const bool valid = q < n;
-	bool observable = false;
-	if (valid) {
-		observable = layer[q].w > 0.0f;
-		if (!observable) {
-			const int x = (int)(q % (uint32_t)width), y = (int)(q / (uint32_t)width);
-			for (int j = max(0, y - half_k); j <= min(height - 1, y + half_k) && !observable; ++j)
-				for (int i = max(0, x - half_k); i <= min(width - 1, x + half_k); ++i)
-					if (layer[j * width + i].w > 0.0f) { observable = true; break; }
-		}
-	}
-	const unsigned m = __ballot_sync(0xffffffffu, observable);
-	if (m) {
-		const unsigned lane = threadIdx.x & 31u;
-		uint32_t base = 0;
-		if (lane == 0) base = atomicAdd(list_count, (uint32_t)__popc(m));
-		base = __shfl_sync(0xffffffffu, base, 0);
-		if (observable) list[base + __popc(m & ((1u << lane) - 1u))] = q;
-	}
-	if (!valid || observable) return;
-	const size_t gq = (size_t)(ty0 + (int)(q / (uint32_t)width)) * full_w + tx0 + (int)(q % (uint32_t)width);
-	Rng rng = rng_states[gq];
-	for (uint32_t i = 0; i < sc.n_lights; ++i)
-		if (sc.lights[i].type == 0) (void)light_sample(sc.lights[i], rng);
-	terms[q] = 1.0f;
 	rng_states[gq] = rng;
 }
 

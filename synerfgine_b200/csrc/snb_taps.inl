@@ -33,9 +33,34 @@ __global__ void __launch_bounds__(128) k_bits_max_pool(uint32_t n_bytes_next_oct
 	next[morton3(x, y, z)] |= bits;
 }
 
+// Parity tap of the generator: state words of subsequence i after curand_init(seed, i, 0) as k_init_rng leaves them, and the first
+// n_uniform draws of rng_uniform from that state (what light_sample / scatter / the lens jitter consume).
+__global__ void __launch_bounds__(128) k_rng_tap(uint32_t n, const Rng* __restrict__ states, uint32_t* __restrict__ out6, float* __restrict__ uniforms, uint32_t n_uniform) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	Rng r = states[i];
+	out6[i * 6 + 0] = r.v0; out6[i * 6 + 1] = r.v1; out6[i * 6 + 2] = r.v2; out6[i * 6 + 3] = r.v3; out6[i * 6 + 4] = r.v4; out6[i * 6 + 5] = r.d;
+	for (uint32_t k = 0; k < n_uniform; ++k) uniforms[(size_t)i * n_uniform + k] = rng_uniform(r);
+}
+
 } // namespace snb
 
 extern "C" {
+
+int snb_rng_tap(snb_ctx* c, uint64_t seed, uint32_t n, uint32_t n_uniform, uint32_t* states6_dev, float* uniforms_dev) {
+	if (!c || !states6_dev || (n_uniform && !uniforms_dev) || n == 0) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	DevBuf tmp;
+	SNB_CUDA(c, tmp.reserve((size_t)n * sizeof(Rng)));
+	k_init_rng<<<(n + 127) / 128, 128, 0, c->stream>>>(n, (unsigned long long)seed, (int)n, 0, 0, (int)n, tmp.as<Rng>());
+	++c->launches;
+	k_rng_tap<<<(n + 127) / 128, 128, 0, c->stream>>>(n, tmp.as<Rng>(), states6_dev, uniforms_dev, n_uniform);
+	++c->launches;
+	const cudaError_t e = cudaStreamSynchronize(c->stream);
+	tmp.release();
+	if (e != cudaSuccess) return c->cuda_fail(e, "snb_rng_tap");
+	return SNB_OK;
+}
 
 int snb_march_trace(snb_ctx* c, const snb_view* view, uint32_t max_samples, float* t_dev, float* dt_dev, uint32_t* cell_dev, uint32_t* n_dev, float* origin_dir_dev) {
 	if (!c || !t_dev || !dt_dev || !cell_dev || !n_dev || max_samples == 0) return SNB_ERR_ARG;
@@ -109,6 +134,28 @@ int snb_get_march_stats(snb_ctx* c, uint64_t* out4) {
 	SNB_CUDA(c, cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
 	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
 	out4[0] = h.iterations; out4[1] = h.dda_steps; out4[2] = h.net_phases; out4[3] = (uint64_t)c->fused_blocks_per_sm * (uint64_t)c->sm_count;
+	return SNB_OK;
+}
+
+int snb_get_alt_status(snb_ctx* c, uint32_t* out132) {
+	if (!c || !out132) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	AltState h;
+	SNB_CUDA(c, cudaMemcpyAsync(&h, c->d_alt.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	out132[0] = h.passes; out132[1] = h.converged; out132[2] = h.last_mismatch; out132[3] = c->alt_target_queries;
+	for (int j = 0; j < kAltSched; ++j) { out132[4 + j] = h.hist[j]; out132[4 + kAltSched + j] = h.sched[j]; }
+	return SNB_OK;
+}
+
+int snb_set_alt_schedule(snb_ctx* c, const uint8_t* steps, uint32_t n) {
+	if (!c || (n && !steps) || n > (uint32_t)kAltSched) return SNB_ERR_ARG;
+	for (uint32_t j = 0; j < n; ++j) if (steps[j] > 8) return c->fail(SNB_ERR_ARG, "batch lengths are 0 (unknown) or 1..8");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	uint8_t sched[kAltSched];
+	for (int j = 0; j < kAltSched; ++j) sched[j] = (uint32_t)j < n ? steps[j] : (n ? (uint8_t)8 : (uint8_t)0);
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_alt.as<unsigned char>() + offsetof(AltState, sched), sched, sizeof sched, cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // `sched` is a stack array
 	return SNB_OK;
 }
 

@@ -41,7 +41,8 @@ def load():
         "orc_grid_layout": (None, [u32, u32, u32, u32, f32, pf, pu32, pu32]),
         "orc_network_inference": (None, [M, pf, u64, pu16, pu16, pu32]),
         "orc_render_nerf": (u64, [M, V, C.c_int, C.c_int, u32, pf, pf, pf, pu16]),
-        "orc_render_nerf_wavefront": (u64, [M, V, C.c_int, C.c_int, pf, pf, pf, pu32, u32]),
+        "orc_render_nerf_wavefront": (u64, [M, V, C.c_int, C.c_int, u32, pf, pf, pf, pu32, pu32, u32]),
+        "orc_render_nerf_sched": (u64, [M, V, C.c_int, C.c_int, pu32, u32, pf, pf, pf]),
         "orc_write_normals": (None, [C.c_int, C.c_int, pf, pf]),
         "orc_accumulate_tonemap": (None, [C.c_int, pf, pf, u32, C.c_int, C.c_int, f32, pf, C.c_int, pf]),
         "orc_tonemap_curve": (None, [pf, C.c_int]),
@@ -76,6 +77,32 @@ def render_nerf(model_desc, view, alt, render_mode=1, steps_per_batch=8, positio
     ns = lib.orc_render_nerf(C.byref(model_desc), C.byref(view), int(alt), render_mode, steps_per_batch, P(fb), P(depth), P(pos) if positions else None, None)
     h, w = view.height, view.width
     return fb.reshape(h, w, 4), depth.reshape(h, w), (pos.reshape(h, w, 3) if positions else None), ns
+
+
+def render_nerf_wavefront(model_desc, view, alt=1, render_mode=1, target_queries=2 * 1024 * 1024, positions=False, cap=256):
+    """Replay of the reference's lock-step march (trace / trace_alt). Returns fb, depth, positions, schedule (S per iteration), alive (n_alive per iteration)."""
+    lib = load()
+    n = view.width * view.height
+    fb = np.zeros((n, 4), np.float32); depth = np.zeros(n, np.float32)
+    pos = np.zeros((n, 3), np.float32) if positions else None
+    sched = np.zeros(cap, np.uint32); alive = np.zeros(cap, np.uint32)
+    lib.orc_render_nerf_wavefront(C.byref(model_desc), C.byref(view), int(alt), render_mode, target_queries, P(fb), P(depth), P(pos) if positions else None,
+                                  P(sched, pu32), P(alive, pu32), cap)
+    k = int(np.count_nonzero(sched))
+    h, w = view.height, view.width
+    return fb.reshape(h, w, 4), depth.reshape(h, w), (pos.reshape(h, w, 3) if positions else None), sched[:k].copy(), alive[:k].copy()
+
+
+def render_nerf_sched(model_desc, view, sched, alt=1, render_mode=1, positions=False):
+    """Per-ray march with an explicit batch-length sequence."""
+    lib = load()
+    n = view.width * view.height
+    fb = np.zeros((n, 4), np.float32); depth = np.zeros(n, np.float32)
+    pos = np.zeros((n, 3), np.float32) if positions else None
+    s = np.ascontiguousarray(sched, np.uint32)
+    lib.orc_render_nerf_sched(C.byref(model_desc), C.byref(view), int(alt), render_mode, P(s, pu32), s.size, P(fb), P(depth), P(pos) if positions else None)
+    h, w = view.height, view.width
+    return fb.reshape(h, w, 4), depth.reshape(h, w), (pos.reshape(h, w, 3) if positions else None)
 
 
 def frame(model_desc, view, scene, rt, rng_seed=1999, n_frames=1):

@@ -34,6 +34,9 @@ def dev(shape, dtype):
     return torch.zeros(shape, dtype=dtype, device="cuda")
 
 
+MARCHES = ["lane"]   # march kernels selectable with snb_set_option(ctx, "march", ...)
+
+
 @pytest.mark.parametrize("kind,w,h,spp,snap", [("small16x2", 96, 64, 0, 1), ("small16x2", 64, 48, 3, 0), ("unit16x2", 64, 64, 0, 1), ("big16x2", 64, 64, 1, 0),
                                                  ("noocc", 32, 32, 0, 1), ("cropped", 96, 64, 0, 1), ("cropped", 64, 48, 2, 0)])
 def test_march_samples_bit_exact(snb, orc, ctx, kind, w, h, spp, snap):
@@ -88,9 +91,9 @@ def test_network_hash_indices_and_outputs(snb, orc, ctx, kind, mlp):
 
 @pytest.mark.parametrize("kind,alt,w,h", [("small16x2", 0, 128, 96), ("small16x2", 1, 128, 96), ("fox8x4", 1, 64, 64), ("unit16x2", 0, 64, 64), ("big16x2", 1, 64, 64),
                                           ("cropped", 1, 96, 64)])
-@pytest.mark.parametrize("march", ["lane", "pool", "tc"])
+@pytest.mark.parametrize("march", MARCHES)
 def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
-    """march: "lane" = one ray per lane + mma.sync MLPs, "pool" = warp ray pool, "tc" = MLPs on tcgen05/TMEM (CTA level)."""
+    """Every march kernel the library offers (MARCHES) against the oracle."""
     m = common.cropped_model() if kind == "cropped" else common.model(kind)
     d = set_model(snb, ctx, m)
     assert snb.snb_set_option(ctx, b"march", march.encode()) == 0
@@ -165,9 +168,13 @@ def test_errors_are_reported_not_thrown(snb, ctx):
 
 
 # ---- BASELINE.json's full size (C2 model, 1920x1080) through size-independent properties ---------------------------------
-def _render_full(snb, ctx, v, tile=None, march=b"lane"):
+def _render_full(snb, ctx, v, tile=None, march=b"lane", alt_schedule=b"fixed"):
+    """sng NeRF layer (positions + normals, no shadows). alt_schedule "fixed" (8 samples per batch) makes a tile and the frame it
+    belongs to march identically whatever their ray counts are — the self-consistency tests below are about tiling, not about
+    the reference's count-dependent batch lengths (those: test_alt_schedule_*)."""
     from synerfgine_b200._lib import Tile
     assert snb.snb_set_option(ctx, b"march", march) == 0
+    assert snb.snb_set_option(ctx, b"alt_schedule", alt_schedule) == 0
     w, h = (tile.w, tile.h) if tile is not None else (v.width, v.height)
     fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
     pos, nrm = dev((h, w, 3), torch.float32), dev((h, w, 3), torch.float32)
@@ -179,14 +186,15 @@ def _render_full(snb, ctx, v, tile=None, march=b"lane"):
     cnt = (C.c_uint64 * 4)()
     assert snb.snb_get_counters(ctx, cnt) == 0
     snb.snb_set_option(ctx, b"march", b"lane")
+    snb.snb_set_option(ctx, b"alt_schedule", b"auto")
     return fb, depth, pos, (int(cnt[0]), int(cnt[1]), int(cnt[2]))
 
 
 def test_full_size_properties(snb, ctx):
     """1080p frame of the benchmark model: (1) two runs are bit-identical (the queue order is not, the result must be);
-    (2) the ray-pool march visits exactly the same samples as the lane march and writes the same bits; (3) the tcgen05 march
-    evaluates the same samples (identical counters) and agrees within the fp16 tolerance; (4) four column strips with the
-    multi-GPU halo reproduce the full frame bit for bit, and their sample counts add up to at least the full frame's."""
+    (2) every other march kernel evaluates the same samples (counters within a sample per ray) and agrees within the fp16 tolerance;
+    (3) four column strips with the multi-GPU halo reproduce the full frame bit for bit, and their sample counts add up to at
+    least the full frame's."""
     from synerfgine_b200._lib import Tile
     from synerfgine_b200 import tiles
     m = common.model("fox16x2")
@@ -197,13 +205,11 @@ def test_full_size_properties(snb, ctx):
     b_fb, b_depth, b_pos, b_cnt = _render_full(snb, ctx, v)
     assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt
     assert a_cnt[0] > 5_000_000 and (a_fb[..., 3] > 0.5).float().mean() > 0.05
-    p_fb, p_depth, p_pos, p_cnt = _render_full(snb, ctx, v, march=b"pool")
-    assert p_cnt == a_cnt
-    assert torch.equal(p_fb, a_fb) and torch.equal(p_depth, a_depth) and torch.equal(p_pos, a_pos)
-    t_fb, t_depth, t_pos, t_cnt = _render_full(snb, ctx, v, march=b"tc")
-    err = (t_fb - a_fb).abs()
-    assert float(err.max()) <= 1e-2 and common.psnr(t_fb.cpu().numpy(), a_fb.cpu().numpy()) >= 50.0
-    assert abs(t_cnt[0] - a_cnt[0]) <= 1e-3 * a_cnt[0] and t_cnt[1] == a_cnt[1]     # a ray may saturate one sample earlier or later
+    for other in MARCHES[1:]:
+        t_fb, t_depth, t_pos, t_cnt = _render_full(snb, ctx, v, march=other.encode())
+        err = (t_fb - a_fb).abs()
+        assert float(err.max()) <= 1e-2 and common.psnr(t_fb.cpu().numpy(), a_fb.cpu().numpy()) >= 50.0
+        assert abs(t_cnt[0] - a_cnt[0]) <= 1e-3 * a_cnt[0] and t_cnt[1] == a_cnt[1]     # a ray may saturate one sample earlier or later
     halo, total = tiles.halo_for(4), 0
     for r in range(4):
         s = tiles.strip_for(r, 4, W, halo)
@@ -243,18 +249,95 @@ def test_camera_that_sees_nothing(snb, ctx):
     assert int(cnt[0]) == 0 and float(fb.abs().max()) == 0.0
 
 
-def test_two_band_ray_generation_is_result_identical(snb, ctx):
-    """Option "bands" = 2 (lower half's rays generated on a side stream while the upper half is marched): same bits."""
+def _alt_status(snb, ctx):
+    st = (C.c_uint32 * 132)()
+    assert snb.snb_get_alt_status(ctx, st) == 0
+    st = list(st)
+    return {"passes": st[0], "converged": st[1], "mismatch": st[2], "alive": np.asarray(st[4:68], np.uint32), "sched": np.asarray(st[68:132], np.uint32)}
+
+
+@pytest.mark.parametrize("kind,w,h,target", [("small16x2", 96, 64, 7800), ("small16x2", 128, 96, 17500), ("fox8x4", 64, 64, 7606)])
+@pytest.mark.parametrize("march", MARCHES)
+def test_alt_schedule_matches_reference_wavefront(snb, orc, ctx, kind, w, h, target, march):
+    """The sng compositor's result depends on the batch lengths S_j = clamp(target / n_alive_j, 1, 8) of the reference's lock-step
+    march (src/testbed_nerf.cu:2189-2190,574). target_n_queries is lowered so that a frame the CPU oracle can replay has short
+    batches at the start, like a 1080p frame has under the real 2^21. After the in-frame passes the library reports the counts
+    n_alive_j and the sequence: both must EQUAL the oracle's replay of the wavefront loop, and the image must meet the bar."""
+    m = common.model(kind)
+    d = set_model(snb, ctx, m)
+    assert snb.snb_set_option(ctx, b"march", march.encode()) == 0
+    assert snb.snb_set_option(ctx, b"alt_schedule", b"auto") == 0
+    assert snb.snb_set_option(ctx, b"alt_target_queries", str(target).encode()) == 0
+    assert snb.snb_set_alt_schedule(ctx, None, 0) == 0                                   # cold start
+    v = common.make_view(w, h)
+    fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    pos, nrm = dev((h, w, 3), torch.float32), dev((h, w, 3), torch.float32)
+    rt = common.default_rt(show_shadow_on_nerf=0)
+    rfb, rdepth, rpos, rsched, ralive = O.render_nerf_wavefront(d, v, alt=1, target_queries=target, positions=True)
+    assert rsched.min() < 8 and len(set(rsched.tolist())) >= 3, f"degenerate test: schedule {rsched}"
+    try:
+        for attempt in range(4):                                                       # a cold start may need more than one call
+            rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(), pos.data_ptr(), nrm.data_ptr())
+            assert rc == 0, snb.snb_last_error(ctx)
+            st = _alt_status(snb, ctx)
+            if st["converged"]:
+                break
+        assert st["converged"] == 1, st
+        k = min(len(rsched), 64)
+        np.testing.assert_array_equal(st["alive"][:k], ralive[:k])                       # n_alive of every lock-step iteration: exact
+        np.testing.assert_array_equal(st["sched"][:k], rsched[:k])
+        a = fb.cpu().numpy()
+        assert common.psnr(a, rfb) >= 50.0 and np.abs(a - rfb).max() <= 1e-2, (common.psnr(a, rfb), np.abs(a - rfb).max())
+        # steady state: the next frame needs one pass
+        rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(), pos.data_ptr(), nrm.data_ptr())
+        assert rc == 0
+        st2 = _alt_status(snb, ctx)
+        assert st2["passes"] == 1 and st2["converged"] == 1
+        assert np.abs(fb.cpu().numpy() - rfb).max() <= 1e-2
+        # and a fixed batch length is a different image (the deviation the option exists to make explicit)
+        assert snb.snb_set_option(ctx, b"alt_schedule", b"fixed") == 0
+        rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(), pos.data_ptr(), nrm.data_ptr())
+        assert rc == 0 and snb.snb_sync(ctx) == 0
+        r8, _, _, _ = O.render_nerf(d, v, 1, positions=True)
+        assert np.abs(fb.cpu().numpy() - r8).max() <= 1e-2
+        assert np.abs(r8 - rfb).max() > 2e-2, "degenerate test: the schedule does not matter for this frame"
+    finally:
+        snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152"); snb.snb_set_option(ctx, b"march", b"lane")
+        snb.snb_set_alt_schedule(ctx, None, 0)
+
+
+def test_alt_schedule_external_tiles_equal_full_frame(snb, ctx):
+    """Multi-GPU form: every tile marches with the sequence of the WHOLE frame (n_alive_j is a whole-frame quantity) and the tiles'
+    counts add up to the frame's; then tiles are bit-identical crops of the frame although their own ray counts are smaller."""
+    from synerfgine_b200._lib import Tile
+    from synerfgine_b200 import tiles
     m = common.model("small16x2")
     set_model(snb, ctx, m)
-    v = common.make_view(320, 288, spp=1, snap=0)
-    assert snb.snb_set_option(ctx, b"bands", b"1") == 0
-    a = _render_full(snb, ctx, v)
-    assert snb.snb_set_option(ctx, b"bands", b"2") == 0
-    b = _render_full(snb, ctx, v)
-    assert snb.snb_set_option(ctx, b"bands", b"1") == 0
-    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and a[3] == b[3]
-    assert a[3][0] > 10000
+    W, H, target = 160, 96, 22000
+    v = common.make_view(W, H, spp=1, snap=0)
+    assert snb.snb_set_option(ctx, b"alt_target_queries", str(target).encode()) == 0
+    try:
+        assert snb.snb_set_alt_schedule(ctx, None, 0) == 0
+        for _ in range(4):
+            full = _render_full(snb, ctx, v, alt_schedule=b"auto")
+            st = _alt_status(snb, ctx)
+            if st["converged"]:
+                break
+        assert st["converged"] == 1 and st["sched"][:8].min() < 8
+        sched = st["sched"].astype(np.uint8)
+        total = np.zeros(64, np.uint64)
+        for r in range(3):
+            s = tiles.strip_for(r, 3, W, 2)
+            assert snb.snb_set_alt_schedule(ctx, sched.ctypes.data_as(C.POINTER(C.c_uint8)), 64) == 0
+            fb, depth, pos, cnt = _render_full(snb, ctx, v, tile=Tile(s.hx0, 0, s.render_width, H), alt_schedule=b"external")
+            assert torch.equal(fb[:, s.crop], full[0][:, s.x0:s.x1]) and torch.equal(depth[:, s.crop], full[1][:, s.x0:s.x1])
+            own = Tile(s.x0, 0, s.x1 - s.x0, H)                                          # counts of the owned columns only (no halo)
+            assert snb.snb_set_alt_schedule(ctx, sched.ctypes.data_as(C.POINTER(C.c_uint8)), 64) == 0
+            _render_full(snb, ctx, v, tile=own, alt_schedule=b"external")
+            total += _alt_status(snb, ctx)["alive"].astype(np.uint64)
+        np.testing.assert_array_equal(total, st["alive"].astype(np.uint64))
+    finally:
+        snb.snb_set_option(ctx, b"alt_target_queries", b"2097152"); snb.snb_set_alt_schedule(ctx, None, 0)
 
 
 def test_snapshot_file_round_trip_renders_the_same_frame(snb, tmp_path):

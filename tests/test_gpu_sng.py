@@ -37,15 +37,45 @@ def dev(shape, dtype=None):
 
 
 def test_xorwow_matches_curand(snb, orc, ctx):
-    """The product seeds with the toolkit's curand_init; the oracle restates XORWOW. Same first draws on every subsequence
-    is checked indirectly: a 1-sample shaded frame below depends on them. Here: the oracle's jump matrix is a permutation-free
-    GF(2) map (full rank proxy: distinct states) and uniforms lie in (0, 1]."""
-    st = np.zeros((64, 6), np.uint32)
-    orc.orc_xorwow_states(1999, 64, O.P(st, O.pu32))
-    assert len({tuple(r) for r in st.tolist()}) == 64
-    u = np.zeros(1000, np.float32)
-    orc.orc_xorwow_uniforms(1999, 5, 1000, O.P(u))
-    assert u.min() > 0 and u.max() <= 1.0 and 0.4 < u.mean() < 0.6
+    """The product seeds its 24-byte generator state with the toolkit's curand_init(seed, subsequence, 0) and draws with its own
+    rng_uniform; the oracle restates XORWOW and the skip-ahead. State words and the first draws of 4096 subsequences, bit for bit
+    (the third leg — curand_uniform of the reference's own init_rand_state on the device — is in test_gpu_refdev.py)."""
+    n, k = 4096, 8
+    st, un = dev((n, 6), torch.int32), dev((n, k))
+    assert snb.snb_rng_tap(ctx, 1999, n, k, st.data_ptr(), un.data_ptr()) == 0, snb.snb_last_error(ctx)
+    rst = np.zeros((n, 6), np.uint32)
+    orc.orc_xorwow_states(1999, n, O.P(rst, O.pu32))
+    np.testing.assert_array_equal(st.cpu().numpy().view(np.uint32), rst)
+    assert len({tuple(r) for r in rst[:64].tolist()}) == 64
+    got = un.cpu().numpy()
+    for sub in (0, 1, 5, 777, n - 1):
+        u = np.zeros(k, np.float32)
+        orc.orc_xorwow_uniforms(1999, sub, k, O.P(u))
+        np.testing.assert_array_equal(got[sub].view(np.uint32), u.view(np.uint32))
+    assert got.min() > 0 and got.max() <= 1.0 and 0.45 < got.mean() < 0.55
+
+
+def test_accumulate_tonemap_matches_oracle(snb, orc, ctx):
+    """accumulate_kernel + tonemap_kernel (src/render_buffer.cu:268-302,569-601) over three samples, every tonemap curve, both colour
+    spaces: the accumulate buffer is a running mean and must carry over from call to call exactly like the oracle's."""
+    rng = np.random.default_rng(3)
+    n = 4099
+    bg = (C.c_float * 4)(0.2, 0.4, 0.1, 0.7)
+    for curve in (0, 1, 2, 3):
+        for cs_srgb, out_srgb in ((0, 1), (1, 1), (0, 0)):
+            acc_d = dev((n, 4)); out_d = dev((n, 4))
+            acc_h = np.zeros((n, 4), np.float32); out_h = np.zeros((n, 4), np.float32)
+            for spp in range(3):
+                frame = rng.random((n, 4)).astype(np.float32) * np.float32(1.5)
+                frame[:, 3] = np.clip(frame[:, 3], 0, 1)
+                fd = torch.from_numpy(frame).cuda()
+                rc = snb.snb_accumulate_tonemap(ctx, n, fd.data_ptr(), acc_d.data_ptr(), spp, cs_srgb, out_srgb, 0.75, bg, curve, out_d.data_ptr())
+                assert rc == 0, snb.snb_last_error(ctx)
+                assert snb.snb_sync(ctx) == 0
+                bgv = np.asarray(list(bg), np.float32)
+                orc.orc_accumulate_tonemap(n, O.P(frame), O.P(acc_h), spp, cs_srgb, out_srgb, 0.75, O.P(bgv), curve, O.P(out_h))
+                np.testing.assert_allclose(acc_d.cpu().numpy(), acc_h, rtol=2e-6, atol=1e-7)      # powf (sRGB transfer) differs in ulps between libm and CUDA
+                np.testing.assert_allclose(out_d.cpu().numpy(), out_h, rtol=2e-5, atol=2e-6)
 
 
 @pytest.mark.parametrize("name", ["c2", "c3"])
@@ -179,16 +209,15 @@ def test_dead_shadow_terms_skip_is_result_identical(snb):
     assert (on[0][0][..., 3] > 0).mean() > 0.05 and (on[0][0][..., 3] == 0).mean() > 0.05   # the frame has both kinds of pixels
 
 
-@pytest.mark.parametrize("opts", [{b"sng_block": b"0", b"terms_block": b"0", b"mesh_priority": b"default", b"terms_compact": b"1"},
-                                  {b"terms_compact": b"1", b"terms_block": b"32", b"lane_warps": b"12"},
+@pytest.mark.parametrize("opts", [{b"sng_block": b"0", b"terms_block": b"0", b"mesh_priority": b"default"},
+                                  {b"terms_block": b"32", b"lane_warps": b"12"},
                                   {b"lane_warps": b"10"},
                                   {b"sng_block": b"32", b"terms_block": b"64"},
-                                  {b"sng_block": b"128", b"terms_block": b"128", b"mesh_after": b"raygen"}])
+                                  {b"sng_block": b"128", b"terms_block": b"128", b"overlap": b"0"}])
 def test_pixel_mapping_and_scheduling_options_are_result_identical(snb, opts):
     """A warp of k_raytrace / k_nerf_shadow_terms covers an 8 x 4 pixel patch (options "sng_block" / "terms_block"; "0" = 32
-    pixels of a row); "terms_compact" queues the observable pixels of the shadow-term pass and runs
-    full warps over the queue; "lane_warps" forces the march's CTA shape (chosen by tile size otherwise);
-    "mesh_priority" / "mesh_after" only move the mesh layer in time. Pixels are independent, so three
+    pixels of a row); "lane_warps" forces the march's CTA shape (chosen by tile size otherwise);
+    "mesh_priority" / "overlap" only move the mesh layer in time. Pixels are independent, so three
     consecutive frames (later ones depend on the generator states left by earlier ones) must have the same bits as the
     defaults — on a frame whose width and height are not multiples of the patch."""
     from synerfgine_b200 import Engine, Testbed
