@@ -223,6 +223,9 @@ int snb_trace_rays(snb_ctx* ctx, const float* rays_dev, uint32_t n, int32_t* obj
 /* ≙ sng::init_rand_state + curand_uniform (src/synerfgine/common.cu:22-34): XORWOW state words {v0..v4, d} of subsequences 0..n-1
  * as the render kernels hold them, and the first n_uniform uniforms each would draw. Synchronises. */
 int snb_rng_tap(snb_ctx* ctx, uint64_t seed, uint32_t n, uint32_t n_uniform, uint32_t* states6_dev, float* uniforms_dev);
+/* Per-level grid scales of the current model as the device evaluates tcnn's grid_scale (exp2f = MUFU.EX2, one FFMA; common_device.h:841-845).
+ * Returns the number of levels written or a negative status. */
+int snb_get_grid_scales(snb_ctx* ctx, float* out_host, uint32_t cap);
 /* Counters of the last NeRF render: [0] network samples, [1] rays launched, [2] rays that hit, [3] march batches. */
 int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
 /* Scheduling statistics of the last NeRF march (instrumentation; SURVEY.md 8d "device counters"): [0] pool iterations summed

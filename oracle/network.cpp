@@ -5,6 +5,9 @@
 
 namespace orc {
 
+static float g_scale_override[32];
+static uint32_t g_scale_override_n = 0;
+
 // tcnn/common_device.h:841-850 grid_scale / grid_resolution; grid.h:692-723 offset table.
 GridLayout make_grid_layout(uint32_t n_levels, uint32_t F, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale) {
 	GridLayout g;
@@ -127,6 +130,12 @@ NetworkView make_network_view(const orc_model& m) {
 	v.rgb_w3 = p; p += 16 * 64;
 	v.grid = p;
 	v.grid_layout = make_grid_layout(m.n_levels, m.n_features_per_level, m.log2_hashmap_size, m.base_resolution, m.per_level_scale);
+	// kernel_grid evaluates grid_scale ON THE DEVICE: exp2f there is MUFU.EX2 and the multiply-subtract is one FFMA (SASS of the
+	// reference build, profiles/r02_refdev_notes.md), which differs from the host's libm value in the last place for most levels. The
+	// hardware function has no host restatement, so GPU parity tests hand its values in (orc_set_grid_scales); the offset table stays the
+	// host's, as in tcnn (grid.h:692-723 runs on the host).
+	if (g_scale_override_n == m.n_levels)
+		for (uint32_t i = 0; i < m.n_levels; ++i) { v.grid_layout.scale[i] = g_scale_override[i]; v.grid_layout.resolution[i] = (uint32_t)std::ceil(g_scale_override[i]) + 1; }
 	return v;
 }
 
@@ -137,6 +146,12 @@ using namespace orc;
 extern "C" {
 
 // Size (in fp16 elements) of the params blob for a model description.
+// Per-level scales as the DEVICE computes them (n = 0 returns to the host formula). See make_network_view.
+void orc_set_grid_scales(const float* scales, uint32_t n) {
+	g_scale_override_n = n <= 32 ? n : 0;
+	for (uint32_t i = 0; i < g_scale_override_n; ++i) g_scale_override[i] = scales[i];
+}
+
 uint64_t orc_n_params(uint32_t n_levels, uint32_t F, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale) {
 	GridLayout g = make_grid_layout(n_levels, F, log2_hashmap_size, base_resolution, per_level_scale);
 	return (uint64_t)(64 * 32 + 16 * 64 + 64 * 32 + 64 * 64 + 16 * 64) + (uint64_t)g.offset[n_levels] * F;

@@ -348,7 +348,9 @@ void ref_nerf_layer(RefEngine* e, RefModel* m, RefScene* s, const RefView& v, co
 	const vec2 focal(v.focal_length[0], v.focal_length[1]);
 	const mat4x3 cam = M43(v.camera);
 	Testbed::NerfTracer tracer;
-	// Testbed::render clears the frame when the camera moved (render_buffer->clear_frame); init_rays clears it as well
+	// Testbed::render clears the frame whenever accumulation restarts (view.render_buffer->clear_frame, testbed.cu:4375-4380); every call
+	// here is such a frame. init_rays_with_payload_kernel_nerf only rewrites rgb, so without this the alpha of a recycled allocation leaks in.
+	CUDA_CHECK_THROW(cudaMemsetAsync(e->nerf_fb.data(), 0, e->nerf_fb.size() * sizeof(vec4), stream));
 	tracer.init_rays_from_camera(v.spp, m->network->padded_output_width(), m->network->n_extra_dims(), res, focal, cam, cam, vec4(0.0f, 0.0f, 0.0f, 1.0f),
 	                             vec2(v.screen_center[0], v.screen_center[1]), vec3(0.0f), (bool)v.snap_to_pixel_centers, m->render_aabb, m->render_aabb_to_local, 0.0f /* near */,
 	                             0.0f /* plane_z: unused outside Slice mode */, 0.0f /* aperture */, Foveation{}, Lens{}, Buffer2DView<const vec4>{}, Buffer2DView<const vec2>{},

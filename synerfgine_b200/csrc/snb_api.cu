@@ -164,7 +164,18 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 		SNB_CUDA(c, c->d_bitfield.reserve(bf_bytes));
 		SNB_CUDA(c, cudaMemcpyAsync(c->d_bitfield.p, m->bitfield, bf_bytes, cudaMemcpyHostToDevice, c->stream));
 	}
-	SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // host staging vectors go out of scope
+	{   // level scales as the device evaluates them (k_grid_scales); resolutions follow, the offset table stays the host's like tcnn's
+		DevBuf tmp;
+		SNB_CUDA(c, tmp.reserve(kMaxLevels * sizeof(float)));
+		float* d_scales = tmp.as<float>();
+		k_grid_scales<<<1, 32, 0, c->stream>>>(L, std::log2(m->per_level_scale), m->base_resolution, d_scales);
+		SNB_LAUNCHED(c);
+		float h_scales[kMaxLevels];
+		SNB_CUDA(c, cudaMemcpyAsync(h_scales, d_scales, L * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+		SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // host staging vectors go out of scope
+		tmp.release();
+		for (uint32_t i = 0; i < L; ++i) { g.scale[i] = h_scales[i]; g.res[i] = (uint32_t)std::ceil(h_scales[i]) + 1; }
+	}
 
 	DevModel& d = c->model;
 	d.grid = g;

@@ -123,6 +123,16 @@ SNB_D int tile_local_index(const DevView& v, uint32_t gidx) {
 	return x + v.tw * y;
 }
 
+// ---- per-level grid scale (once per model) -------------------------------------------------------------------------------------
+// tcnn's kernel_grid evaluates grid_scale(level, log2_per_level_scale, base_resolution) = exp2f(level * log2_pls) * base - 1 on the
+// device in every thread (common_device.h:841-845): exp2f is MUFU.EX2 there and nvcc contracts the multiply-subtract into one FFMA.
+// The host's libm value differs in the last place on most levels, which moves ~17 % of the fp16 features by an ulp, so the scales
+// are evaluated here once, by the same two operations, and kept in the level table.
+__global__ void k_grid_scales(uint32_t n_levels, float log2_per_level_scale, uint32_t base_resolution, float* __restrict__ out) {
+	const uint32_t level = threadIdx.x;
+	if (level < n_levels) out[level] = fmaf(exp2f((float)level * log2_per_level_scale), (float)base_resolution, -1.0f);
+}
+
 // ---- coarse look-ahead grid (once per model) ------------------------------------------------------------------------
 // One thread per bitfield byte of cascades 0..max_mip; every set bit marks the coarse cells its world box touches,
 // dilated by one coarse cell so that a DDA grazing a cell corner can never miss it.

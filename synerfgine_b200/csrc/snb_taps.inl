@@ -159,6 +159,15 @@ int snb_set_alt_schedule(snb_ctx* c, const uint8_t* steps, uint32_t n) {
 	return SNB_OK;
 }
 
+int snb_get_grid_scales(snb_ctx* c, float* out_host, uint32_t cap) {
+	if (!c || !out_host) return SNB_ERR_ARG;
+	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model");
+	const uint32_t n = c->model.grid.n_levels;
+	if (cap < n) return c->fail(SNB_ERR_ARG, "snb_get_grid_scales: buffer too small");
+	for (uint32_t i = 0; i < n; ++i) out_host[i] = c->model.grid.scale[i];
+	return (int)n;
+}
+
 int snb_get_stage_ms(snb_ctx* c, float* out5) {
 	if (!c || !out5) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));

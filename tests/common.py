@@ -80,3 +80,16 @@ def default_rt(**kw):
         assert hasattr(rt, k), k
         setattr(rt, k, v)
     return rt
+
+
+def use_device_grid_scales(snb, ctx):
+    """tcnn's kernel_grid evaluates grid_scale on the device (exp2f = MUFU.EX2, one FFMA); the product does the same once per model
+    (k_grid_scales). The oracle cannot restate a hardware function, so it is handed those <= 32 floats for bit-exact feature comparisons;
+    their correctness is pinned by the reference's own kernel_grid (tests/test_gpu_refdev.py::test_hash_grid_features_bit_exact)."""
+    import oracle_lib
+    sc = (C.c_float * 32)()
+    n = snb.snb_get_grid_scales(ctx, sc, 32)
+    assert n > 0, snb.snb_last_error(ctx)
+    arr = np.asarray(list(sc)[:n], np.float32)
+    oracle_lib.load().orc_set_grid_scales(arr.ctypes.data_as(C.POINTER(C.c_float)), n)
+    return arr

@@ -23,3 +23,13 @@ def snb():
 def orc():
     import oracle_lib
     return oracle_lib.load()
+
+
+@pytest.fixture(autouse=True)
+def _oracle_host_scales(request):
+    """GPU parity tests hand the device-evaluated grid scales to the oracle (common.use_device_grid_scales); every test starts and ends
+    on the oracle's own host formula."""
+    yield
+    if request.node.get_closest_marker("gpu") is not None:
+        import oracle_lib
+        oracle_lib.load().orc_set_grid_scales(None, 0)

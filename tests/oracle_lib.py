@@ -37,6 +37,7 @@ def load():
         "orc_mip_from_pos": (u32, [pf]),
         "orc_march_to_occupied": (f32, [M, pf, pf, f32]),
         "orc_init_ray": (None, [V, M, u32, u32, pf]),
+        "orc_set_grid_scales": (None, [pf, u32]),
         "orc_n_params": (u64, [u32, u32, u32, u32, f32]),
         "orc_grid_layout": (None, [u32, u32, u32, u32, f32, pf, pu32, pu32]),
         "orc_network_inference": (None, [M, pf, u64, pu16, pu16, pu32]),

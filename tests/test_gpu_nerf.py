@@ -27,6 +27,7 @@ def set_model(snb, ctx, m):
     d = m.desc()
     rc = snb.snb_set_model(ctx, C.byref(d))
     assert rc == 0, snb.snb_last_error(ctx)
+    common.use_device_grid_scales(snb, ctx)
     return d
 
 

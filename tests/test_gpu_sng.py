@@ -107,6 +107,7 @@ def test_bvh_hit_ids_bit_exact(snb, orc, ctx, name):
 def frame_pair(snb, ctx, name, w, h, n_frames=1, **rt_over):
     m = common.model("small16x2")
     d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
+    common.use_device_grid_scales(snb, ctx)
     sc = load_scene(snb, ctx, name)
     rt = sc.rt.copy()
     for k, v in rt_over.items():
