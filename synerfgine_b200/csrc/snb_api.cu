@@ -46,7 +46,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 	const std::string k(key), v(value);
 	if (k == "march") {
 		if (v == "lane") c->march_variant = 3;
-		else return c->fail(SNB_ERR_ARG, "march: expected lane");
+		else if (v == "ws") c->march_variant = 6;
+		else return c->fail(SNB_ERR_ARG, "march: expected ws | lane");
 	} else if (k == "alt_schedule") {
 		if (v == "auto") c->alt_mode = 0;
 		else if (v == "external") c->alt_mode = 1;

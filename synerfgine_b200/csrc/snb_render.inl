@@ -38,7 +38,25 @@ static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int re
 }
 
 template <int F, bool ALT>
+static int launch_ws(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
+	const int slot = (F == 1 ? 0 : F == 2 ? 1 : F == 4 ? 2 : 3) * 2 + (ALT ? 1 : 0);
+	if (!c->ws_ready[slot]) {
+		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_ws<F, ALT>, cudaFuncAttributeMaxDynamicSharedMemorySize, ws::kSmemAlloc));
+		c->ws_ready[slot] = true;
+	}
+	c->fused_blocks_per_sm = 1;
+	const int slots = ws::kGroups * ws::kRows;   // ray slots per CTA
+	const int blocks = std::max(1, std::min(c->sm_count, (n_px + slots - 1) / slots));
+	k_nerf_march_ws<F, ALT><<<blocks, ws::kThreads, ws::kSmemAlloc, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt);
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
+template <int F, bool ALT>
 static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
+	// "ws": warp-specialised tcgen05 pipeline (default). The stock path's Positions / Depth visualisations need the sample position in
+	// the compositor, which only the lane kernel carries.
+	if (c->march_variant == 6 && (ALT || (render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH))) return launch_ws<F, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
 	// CTA shape by the rays a lane will see (option "lane_warps": 0 = by tile size, else 10 | 12): results do not depend on it
 	const bool few = c->lane_warps ? c->lane_warps == kFusedWarpsFew : (size_t)n_px < (size_t)c->sm_count * SNB_LANE_CTAS * kFusedWarps * 32 * 16;
 	return few ? launch_lane<F, ALT, kFusedWarpsFew>(c, dv, out, render_mode, n_px, queue, qctl, alt) : launch_lane<F, ALT, kFusedWarps>(c, dv, out, render_mode, n_px, queue, qctl, alt);

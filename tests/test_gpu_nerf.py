@@ -35,7 +35,7 @@ def dev(shape, dtype):
     return torch.zeros(shape, dtype=dtype, device="cuda")
 
 
-MARCHES = ["lane"]   # march kernels selectable with snb_set_option(ctx, "march", ...)
+MARCHES = ["ws", "lane"]   # march kernels selectable with snb_set_option(ctx, "march", ...); the first one is the default
 
 
 @pytest.mark.parametrize("kind,w,h,spp,snap", [("small16x2", 96, 64, 0, 1), ("small16x2", 64, 48, 3, 0), ("unit16x2", 64, 64, 0, 1), ("big16x2", 64, 64, 1, 0),
@@ -109,7 +109,7 @@ def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
         rc = snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr())
     assert rc == 0, snb.snb_last_error(ctx)
     rc = snb.snb_sync(ctx)
-    snb.snb_set_option(ctx, b"march", b"lane")
+    snb.snb_set_option(ctx, b"march", MARCHES[0].encode())
     assert rc == 0, snb.snb_last_error(ctx)
     rfb, rdepth, rpos, ns = O.render_nerf(d, v, alt, positions=bool(alt))
     a = fb.cpu().numpy()
@@ -124,7 +124,7 @@ def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
     assert snb.snb_get_counters(ctx, cnt) == 0
     # network samples: the oracle (like the reference) evaluates whole 8-step batches and discards what follows a saturated
     # sample; the fused kernel composites step by step and never evaluates those, so it does the same or less work.
-    assert 0.85 * ns <= int(cnt[0]) <= ns + 8, (cnt[0], ns)
+    assert 0.85 * ns <= int(cnt[0]) <= ns + 8, (cnt[0], ns)   # counted: samples composited (both kernels)
     if alt:
         pd = np.abs(pos.cpu().numpy() - rpos)
         assert (pd.max(-1) > 0.05).mean() < 2e-3
@@ -169,7 +169,7 @@ def test_errors_are_reported_not_thrown(snb, ctx):
 
 
 # ---- BASELINE.json's full size (C2 model, 1920x1080) through size-independent properties ---------------------------------
-def _render_full(snb, ctx, v, tile=None, march=b"lane", alt_schedule=b"fixed"):
+def _render_full(snb, ctx, v, tile=None, march=MARCHES[0].encode(), alt_schedule=b"fixed"):
     """sng NeRF layer (positions + normals, no shadows). alt_schedule "fixed" (8 samples per batch) makes a tile and the frame it
     belongs to march identically whatever their ray counts are — the self-consistency tests below are about tiling, not about
     the reference's count-dependent batch lengths (those: test_alt_schedule_*)."""
@@ -186,7 +186,7 @@ def _render_full(snb, ctx, v, tile=None, march=b"lane", alt_schedule=b"fixed"):
     assert snb.snb_sync(ctx) == 0, snb.snb_last_error(ctx)
     cnt = (C.c_uint64 * 4)()
     assert snb.snb_get_counters(ctx, cnt) == 0
-    snb.snb_set_option(ctx, b"march", b"lane")
+    snb.snb_set_option(ctx, b"march", MARCHES[0].encode())
     snb.snb_set_option(ctx, b"alt_schedule", b"auto")
     return fb, depth, pos, (int(cnt[0]), int(cnt[1]), int(cnt[2]))
 
@@ -204,7 +204,7 @@ def test_full_size_properties(snb, ctx):
     v = common.make_view(W, H, spp=1, snap=0)
     a_fb, a_depth, a_pos, a_cnt = _render_full(snb, ctx, v)
     b_fb, b_depth, b_pos, b_cnt = _render_full(snb, ctx, v)
-    assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt
+    assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt   # counters = samples COMPOSITED ("ws" also evaluates, and ignores, the one or two in flight when a ray saturates)
     assert a_cnt[0] > 5_000_000 and (a_fb[..., 3] > 0.5).float().mean() > 0.05
     for other in MARCHES[1:]:
         t_fb, t_depth, t_pos, t_cnt = _render_full(snb, ctx, v, march=other.encode())
@@ -303,7 +303,7 @@ def test_alt_schedule_matches_reference_wavefront(snb, orc, ctx, kind, w, h, tar
         assert np.abs(fb.cpu().numpy() - r8).max() <= 1e-2
         assert np.abs(r8 - rfb).max() > 2e-2, "degenerate test: the schedule does not matter for this frame"
     finally:
-        snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152"); snb.snb_set_option(ctx, b"march", b"lane")
+        snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152"); snb.snb_set_option(ctx, b"march", MARCHES[0].encode())
         snb.snb_set_alt_schedule(ctx, None, 0)
 
 
