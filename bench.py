@@ -240,6 +240,7 @@ def run_ours(args, rank, local_rank, world):
                 stage_acc[k_] = stage_acc.get(k_, 0.0) + v_ / K
             c = tb.counters(); samples += c["samples"]; rays += c["rays"]
             march_stats = tb.march_stats()
+            march_stats["ws_pipeline"] = {k_: round(float(v_), 4) for k_, v_ in tb.ws_profile().items()}
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()

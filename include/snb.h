@@ -233,6 +233,10 @@ int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
 /* Scheduling statistics of the last NeRF march (instrumentation; SURVEY.md 8d "device counters"): [0] pool iterations summed
  * over CTAs, [1] empty-space DDA steps, [2] search passes (warp level), [3] CTAs of the persistent grid. */
 int snb_get_march_stats(snb_ctx* ctx, uint64_t* out4_host);
+/* Pipeline balance of the last "ws" march (SM cycles summed over warps): [0] producer warps' lifetime, [1] waiting for a free operand stage,
+ * [2] in the group barrier, [3] empty-space search, [4] sample set-up + hash-grid gather + publish, [5] tiles published (per producer warp,
+ * summed), [6] epilogue warps' lifetime, [7] epilogue warps waiting for the tensor core. */
+int snb_get_ws_profile(snb_ctx* ctx, uint64_t* out8_host);
 /* Device time (ms, CUDA events on the context's stream) of the stages of the last frame: [0] NeRF ray generation,
  * [1] fused NeRF march kernel, [2] normals + mesh shadows on the NeRF, [3] mesh layer, [4] overlay. Synchronises. */
 int snb_get_stage_ms(snb_ctx* ctx, float* out5_host);

@@ -86,6 +86,7 @@ SIGNATURES = {
     "snb_get_counters": (C.c_int, [vp, C.POINTER(u64)]),
     "snb_get_march_stats": (C.c_int, [vp, C.POINTER(u64)]),
     "snb_get_stage_ms": (C.c_int, [vp, pf32]),
+    "snb_get_ws_profile": (C.c_int, [vp, C.POINTER(u64)]),
     "snb_get_grid_scales": (C.c_int, [vp, pf32, u32]),
     "snb_rng_tap": (C.c_int, [vp, u64, u32, u32, vp, vp]),
     "snb_get_alt_status": (C.c_int, [vp, C.POINTER(u32)]),

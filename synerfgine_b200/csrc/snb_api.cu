@@ -107,8 +107,8 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	}
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
-	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(sizeof(NerfCounters)) != cudaSuccess || c->d_alt.reserve(sizeof(AltState)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
-	cudaMemsetAsync(c->d_counters.p, 0, sizeof(NerfCounters), c->stream);
+	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(2 * sizeof(NerfCounters)) != cudaSuccess || c->d_alt.reserve(sizeof(AltState)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
+	cudaMemsetAsync(c->d_counters.p, 0, 2 * sizeof(NerfCounters), c->stream);
 	cudaMemsetAsync(c->d_alt.p, 0, sizeof(AltState), c->stream);
 	memset(&c->model, 0, sizeof c->model);
 	*out = c;

@@ -94,7 +94,7 @@ struct Acc { uint32_t ray; uint32_t fin; float r, g, b, a, depth, maxw; };
 template <int F, bool ALT>
 __global__ void __launch_bounds__(ws::kThreads, 1)
 k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
-                unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters, AltCtl alt) {
+                unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters, AltCtl alt, unsigned long long* __restrict__ prof) {
 	using namespace ws;
 	if (alt.conditional && !alt.st->redo) return;   // later pass of the batch-schedule iteration: only after a mismatch (uniform)
 	extern __shared__ unsigned char smem_dyn[];
@@ -153,6 +153,8 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 		int k = 0, n_empty = 0;
 		bool alive = false, drained = false;
 		uint32_t use = 0;                                           // tiles this group has published
+		long long t_wait = 0, t_bar = 0, t_search = 0, t_enc = 0;   // pipeline balance (prof): where a producer warp's time goes
+		const long long t_begin = clock64();
 		for (;;) {
 			if (alive && s_done[g * kRows + row] == ray) alive = false;   // the epilogue saturated this ray: drop it (samples in flight are ignored there)
 			// -- refill: one atomic per warp ------------------------------------------------------------------------------------------
@@ -175,7 +177,10 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 			const uint32_t stage = use & 1u;
 			unsigned char* f_tile = smem + kOffF + (g * kStages + stage) * kTileF;
 			RowMeta* meta = reinterpret_cast<RowMeta*>(smem + kOffMeta) + (g * kStages + stage) * kRows + row;
-			if (!group_any(g, alive)) {
+			long long c0 = clock64();
+			const bool any_alive = group_any(g, alive);
+			long long c1 = clock64(); t_bar += c1 - c0;
+			if (!any_alive) {
 				// the whole group is out of work: hand the consumer a terminate tile and leave
 				tc::mbar_wait(bar(kBarEmpty + g * kStages + stage), ((use >> 1) & 1u) ^ 1u);
 				if (row == 0) s_hdr[g * kStages + stage] = kTerminate;
@@ -207,11 +212,13 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 					if (__popc(__ballot_sync(0xFFFFFFFFu, valid)) >= kMinFill) break;
 				}
 			}
+			c0 = clock64(); t_search += c0 - c1;
 			// a ray that dies in the last possible lock-step iteration is never compacted into the hit list (src/testbed_nerf.cu:2165-2271)
 			const uint32_t nowrite = (step_i + batch_steps >= kMarchIter) ? (uint32_t)kNoWrite : 0u;
 			if (end_flags == kEnd && nowrite) end_flags = kDrop;
 			// -- publish this lane's row of the tile --------------------------------------------------------------------------------
 			tc::mbar_wait(bar(kBarEmpty + g * kStages + stage), ((use >> 1) & 1u) ^ 1u);
+			c1 = clock64(); t_wait += c1 - c0;
 			RowMeta rec; rec.dt = 0.0f; rec.depth = 0.0f; rec.ray = ray; rec.flags = end_flags;
 			if (valid) {
 				const float dt = step_size_call(t, env.st);
@@ -237,6 +244,11 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 			tc::fence_async_smem();                                                       // generic-proxy writes -> visible to the tensor core's async proxy
 			mbar_arrive(bar(kBarFull + g * kStages + stage));
 			++use;
+			t_enc += clock64() - c1;
+		}
+		if (prof && lane == 0) {
+			atomicAdd(prof + 0, (unsigned long long)(clock64() - t_begin)); atomicAdd(prof + 1, (unsigned long long)t_wait); atomicAdd(prof + 2, (unsigned long long)t_bar);
+			atomicAdd(prof + 3, (unsigned long long)t_search); atomicAdd(prof + 4, (unsigned long long)t_enc); atomicAdd(prof + 5, (unsigned long long)use);
 		}
 	} else if (warp < kMmaWarp) {
 		// ===== EPILOGUE ==========================================================================================================
@@ -246,8 +258,10 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 		unsigned char* r_buf = smem + kOffR + c * kRows * 32 * 2;
 		Acc acc0 = {0xFFFFFFFFu, 0u, 0, 0, 0, 0, 0, 0}, acc1 = acc0;
 		uint32_t par_mma = 0;
+		long long t_idle = 0;
+		const long long t_begin = clock64();
 		auto layer_done = [&]() { tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(bar(kBarEpi + c)); };
-		auto await_mma = [&]() { mbar_wait_long(bar(kBarMma + c), par_mma); par_mma ^= 1u; tc::fence_after_sync(); };
+		auto await_mma = [&]() { const long long w0 = clock64(); mbar_wait_long(bar(kBarMma + c), par_mma); par_mma ^= 1u; tc::fence_after_sync(); t_idle += clock64() - w0; };
 		for (;;) {
 			await_mma();                                                                  // layer 1 of a new tile, or the exit signal
 			const uint32_t info = s_info[c];
@@ -329,6 +343,7 @@ k_nerf_march_ws(DevModel model, DevView view, NerfOut out, int render_mode, cons
 				}
 			}
 		}
+		if (prof && lane == 0) { atomicAdd(prof + 6, (unsigned long long)(clock64() - t_begin)); atomicAdd(prof + 7, (unsigned long long)t_idle); }
 	} else if (lane == 0) {
 		// ===== MMA ISSUER (one thread) ============================================================================================
 		const uint32_t sW = tc::smem_u32(smem + kOffW);

@@ -47,7 +47,8 @@ static int launch_ws(snb_ctx* c, const DevView& dv, const NerfOut& out, int rend
 	c->fused_blocks_per_sm = 1;
 	const int slots = ws::kGroups * ws::kRows;   // ray slots per CTA
 	const int blocks = std::max(1, std::min(c->sm_count, (n_px + slots - 1) / slots));
-	k_nerf_march_ws<F, ALT><<<blocks, ws::kThreads, ws::kSmemAlloc, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt);
+	k_nerf_march_ws<F, ALT><<<blocks, ws::kThreads, ws::kSmemAlloc, c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt,
+	                                                                                 reinterpret_cast<unsigned long long*>(&c->d_counters.as<NerfCounters>()[1]));
 	SNB_LAUNCHED(c);
 	return SNB_OK;
 }
@@ -83,7 +84,7 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	const int n_px = dv.tw * dv.th;
 	SNB_CUDA(c, c->d_queue.reserve(((size_t)n_px + 64) * sizeof(RayRec)));
 	SNB_CUDA(c, cudaMemsetAsync(c->d_qctl.p, 0, 16, c->stream));
-	SNB_CUDA(c, cudaMemsetAsync(c->d_counters.p, 0, sizeof(NerfCounters), c->stream));
+	SNB_CUDA(c, cudaMemsetAsync(c->d_counters.p, 0, 2 * sizeof(NerfCounters), c->stream));   // counters + pipeline-balance cycles of the ws march
 	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches_x = (dv.tw + 7) / 8, patches_y = (dv.th + 3) / 4;

@@ -168,6 +168,14 @@ int snb_get_grid_scales(snb_ctx* c, float* out_host, uint32_t cap) {
 	return (int)n;
 }
 
+int snb_get_ws_profile(snb_ctx* c, uint64_t* out8) {
+	if (!c || !out8) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, cudaMemcpyAsync(out8, &c->d_counters.as<NerfCounters>()[1], 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	return SNB_OK;
+}
+
 int snb_get_stage_ms(snb_ctx* c, float* out5) {
 	if (!c || !out5) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));

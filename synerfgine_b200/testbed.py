@@ -171,6 +171,14 @@ class Testbed:
         self._check(self.lib.snb_get_march_stats(self.ctx, out), "snb_get_march_stats")
         return {"pool_iterations": out[0], "dda_steps": out[1], "search_passes": out[2], "ctas": out[3]}
 
+    def ws_profile(self):
+        """Pipeline balance of the last "ws" march as fractions of the warps' lifetime (snb_get_ws_profile)."""
+        o = (C.c_uint64 * 8)()
+        self._check(self.lib.snb_get_ws_profile(self.ctx, o), "snb_get_ws_profile")
+        p, e = max(1, o[0]), max(1, o[6])
+        return {"producer_wait_stage": o[1] / p, "producer_group_barrier": o[2] / p, "producer_search": o[3] / p, "producer_encode_publish": o[4] / p,
+                "tiles_per_producer_warp": o[5] / 16.0, "epilogue_wait_tensor_core": o[7] / e, "producer_cycles_per_tile": o[0] / max(1, o[5])}
+
     def stage_ms(self):
         """Device time of the last frame's stages (synchronises): nerf_raygen, nerf_march, nerf_post, mesh, overlay."""
         out = (C.c_float * 5)()
