@@ -253,6 +253,11 @@ int snb_scene_get(const snb_scene* s, snb_object* objects, snb_material* materia
 /* camera block: view dir, look-at, zoom, vo_scale + keyframe path; frame index advances CamPath (cam_path.cuh:116-142). */
 int snb_scene_camera(const snb_scene* s, float* view3, float* at3, float* zoom, float* vo_scale, uint32_t* n_keyframes);
 int snb_scene_camera_at(const snb_scene* s, uint32_t frame, uint32_t total_frames, float* view3, float* at3, float* zoom);
+/* ≙ Engine::resize (engine.cu:236-255): resolutions of the NeRF layer and the mesh layer for a window, and syn_px_scale, from the scene's
+ * "res_factor" and "vo_scale". */
+int snb_scene_resolution(const snb_scene* s, int window_w, int window_h, int* nerf_w, int* nerf_h, int* syn_w, int* syn_h, int* syn_px_scale);
+/* CamPath / animation switches: frames of the path, "move_on_start", "animation_speed" > 0, "res_factor". */
+int snb_scene_path_info(const snb_scene* s, uint32_t* total_frames, int32_t* playing, int32_t* animations, int32_t* res_factor);
 /* ≙ Testbed::reset_camera + set_view_dir + set_look_at + set_scale (src/testbed.cu:405-425,470-492) as Engine::init
  * applies the JSON camera block (engine.cu:148-151): camera matrix (mat4x3, column-major) out. */
 int snb_camera_from_view(const float* view3, const float* at3, float zoom, float* out12);

@@ -100,6 +100,8 @@ SIGNATURES = {
     "snb_scene_camera_at": (C.c_int, [vp, u32, u32, pf32, pf32, pf32]),
     "snb_camera_from_view": (C.c_int, [pf32, pf32, f32, pf32]),
     "snb_scene_advance": (C.c_int, [vp]),
+    "snb_scene_resolution": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "snb_scene_path_info": (C.c_int, [vp, C.POINTER(u32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
     "snb_bvh_build": (C.c_int, [pf32, i32, i32, pf32, i32, C.POINTER(i32)]),
     "snb_obj_load": (C.c_int, [C.c_char_p, pf32, i32, C.POINTER(i32)]),
     "snb_density_to_bitfield": (C.c_int, [vp, pf32, u32, C.POINTER(u8)]),

@@ -148,7 +148,7 @@ struct snb_scene {
 	std::vector<LightAnim> light_anim;
 	snb_rt_params rt;
 	// camera block
-	v3 view_dir, at_pos; float zoom; int vo_scale; float anim_speed; bool animations;
+	v3 view_dir, at_pos; float zoom; int vo_scale; float anim_speed; bool animations; bool playing; int res_factor;
 	std::vector<Keyframe> keyframes; int total_time_ms, fps, total_frames, frames_between;
 };
 
@@ -180,7 +180,7 @@ int snb_scene_load_json(const char* json_text, const char* base_dir, snb_scene**
 	*out = nullptr;
 	std::unique_ptr<snb_scene> sc(new snb_scene());
 	default_rt(sc->rt);
-	sc->view_dir = mk3(0, 0, 0); sc->at_pos = mk3(0, 0, 0); sc->zoom = 1.0f; sc->vo_scale = 4; sc->anim_speed = 1.0f; sc->animations = false;
+	sc->view_dir = mk3(0, 0, 0); sc->at_pos = mk3(0, 0, 0); sc->zoom = 1.0f; sc->vo_scale = 4; sc->anim_speed = 1.0f; sc->animations = false; sc->playing = false; sc->res_factor = 64;   // Testbed::m_fixed_res_factor default (engine.cuh:122)
 	sc->total_time_ms = 10000; sc->fps = 24; sc->total_frames = 0; sc->frames_between = 1;
 	try {
 		snbjson::Ptr root = snbjson::parse(json_text);
@@ -197,6 +197,7 @@ int snb_scene_load_json(const char* json_text, const char* base_dir, snb_scene**
 				if (cam.has("frames")) for (size_t i = 0; i < cam.at("frames").size(); ++i) { const auto& k = cam.at("frames").at(i); sc->keyframes.push_back({jv3(k.at("view")), jv3(k.at("at")), k.at("zoom").f()}); }
 				if (cam.has("total_time_ms")) sc->total_time_ms = cam.at("total_time_ms").i();
 				if (cam.has("fps")) sc->fps = cam.at("fps").i();
+				if (cam.has("move_on_start")) sc->playing = cam.at("move_on_start").boolean();
 				sc->total_frames = sc->total_time_ms * sc->fps / 1000;
 				for (size_t i = 0; i < cam.at("path").size(); ++i) { const auto& k = cam.at("path").at(i); sc->keyframes.push_back({jv3(k.at("view")), jv3(k.at("at")), k.at("zoom").f()}); }
 				sc->frames_between = sc->total_frames / std::max((int)sc->keyframes.size() - 1, 1);
@@ -219,7 +220,8 @@ int snb_scene_load_json(const char* json_text, const char* base_dir, snb_scene**
 			if (r.has("show_nerf")) rt.show_nerf = r.at("show_nerf").boolean();
 			if (r.has("syn_filter")) rt.buffer_type = buffer_type_of(r.at("syn_filter").s());
 			if (r.has("depth_offset")) rt.depth_offset = r.at("depth_offset").f();
-			// res_factor, clear_color, smooth_threshold, attenuation, show_light_pos, max_shadow_variance, nerf_ao_intensity,
+			if (r.has("res_factor")) sc->res_factor = std::max(1, (int)r.at("res_factor").i());
+			// clear_color, smooth_threshold, attenuation, show_light_pos, max_shadow_variance, nerf_ao_intensity,
 			// show_virtual_obj, nerf_filter: read by the reference but without effect on this path (or GUI-only).
 		}
 		const snbjson::Value& mats = cfg.at("materials");
@@ -333,6 +335,32 @@ int snb_scene_camera_at(const snb_scene* s, uint32_t frame, uint32_t total_frame
 	if (view3) { view3[0] = v.x; view3[1] = v.y; view3[2] = v.z; }
 	if (at3) { at3[0] = at.x; at3[1] = at.y; at3[2] = at.z; }
 	if (zoom) *zoom = invk * a.zoom + k * b.zoom;
+	return SNB_OK;
+}
+
+// Engine::resize (engine.cu:236-255): the NeRF layer renders at window * min(1, 8 / res_factor) (clamped to [window / 16, window]), the mesh
+// layer at min(nerf_res * vo_scale, window); syn_px_scale = mesh width / NeRF width. res_factor 8 (every BASELINE config) gives equal
+// resolutions and scale 1.
+int snb_scene_resolution(const snb_scene* s, int window_w, int window_h, int* nerf_w, int* nerf_h, int* syn_w, int* syn_h, int* syn_px_scale) {
+	if (!s || window_w <= 0 || window_h <= 0) return SNB_ERR_ARG;
+	const float factor = std::min(1.0f, 8.0f / (float)s->res_factor);
+	auto clampi = [](int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); };
+	const int nw = clampi((int)((float)window_w * factor), window_w / 16, window_w), nh = clampi((int)((float)window_h * factor), window_h / 16, window_h);
+	const float vs = (float)s->vo_scale;
+	const int rw = std::min(clampi((int)((float)nw * vs), nw / 16, nw * 16), window_w), rh = std::min(clampi((int)((float)nh * vs), nh / 16, nh * 16), window_h);
+	if (nerf_w) *nerf_w = nw; if (nerf_h) *nerf_h = nh; if (syn_w) *syn_w = rw; if (syn_h) *syn_h = rh;
+	if (syn_px_scale) *syn_px_scale = std::max(1, rw / std::max(1, nw));
+	return SNB_OK;
+}
+
+// CamPath / animation switches of the scene: total_frames = total_time_ms * fps / 1000, playing = "move_on_start", animations =
+// "animation_speed" > 0 (engine.cu:43-45; cam_path.cuh:98-115).
+int snb_scene_path_info(const snb_scene* s, uint32_t* total_frames, int32_t* playing, int32_t* animations, int32_t* res_factor) {
+	if (!s) return SNB_ERR_ARG;
+	if (total_frames) *total_frames = (uint32_t)std::max(0, s->total_frames);
+	if (playing) *playing = s->playing ? 1 : 0;
+	if (animations) *animations = s->animations ? 1 : 0;
+	if (res_factor) *res_factor = s->res_factor;
 	return SNB_OK;
 }
 

@@ -23,6 +23,17 @@ class Scene:
         view = (C.c_float * 3)(); at = (C.c_float * 3)(); zoom = C.c_float(); vo = C.c_float(); nk = C.c_uint32()
         self.lib.snb_scene_camera(self.handle, view, at, C.byref(zoom), C.byref(vo), C.byref(nk))
         self.view_dir, self.at_pos, self.zoom, self.vo_scale, self.n_keyframes = list(view), list(at), zoom.value, vo.value, nk.value
+        tf, pl, an, rf = C.c_uint32(), C.c_int32(), C.c_int32(), C.c_int32()
+        self.lib.snb_scene_path_info(self.handle, C.byref(tf), C.byref(pl), C.byref(an), C.byref(rf))
+        self.total_frames, self.move_on_start, self.animations, self.res_factor = tf.value, bool(pl.value), bool(an.value), rf.value
+
+    def resolution(self, window_w, window_h):
+        """≙ Engine::resize: (nerf_w, nerf_h, syn_w, syn_h, syn_px_scale) for a window, from "res_factor" and "vo_scale"."""
+        o = [C.c_int() for _ in range(5)]
+        rc = self.lib.snb_scene_resolution(self.handle, window_w, window_h, *[C.byref(x) for x in o])
+        if rc != 0:
+            raise _lib.SnbError("snb_scene_resolution")
+        return tuple(x.value for x in o)
 
     @classmethod
     def from_file(cls, path, base_dir=None):

@@ -75,7 +75,7 @@ def scene_c3(animated=False):
     """C3/C4: armadillo + bunny + monkey, lambertian + glossy, point + directional light, depth 2, light_samples 4, lens > 0."""
     anim = (lambda: {"rot_center": [0.5, 0.4, 0.5], "rot_axis": [0.0, 1.0, 0.0], "rot_angle": 0.1}) if animated else (lambda: None)
     cam = dict(CAMERA)
-    cam.update({"fps": 24, "total_time_ms": 1000, "animation_speed": 1.0 if animated else 0.0,
+    cam.update({"fps": 24, "total_time_ms": 1000, "animation_speed": 1.0 if animated else 0.0, "move_on_start": bool(animated),
                 "path": [{"view": v, "at": CAMERA["at"], "zoom": CAMERA["zoom"]} for v in ORBIT]})
     return {
         "camera": cam,

@@ -199,14 +199,23 @@ class Engine:
         self.width = self.height = 0
         self.frame_index = 0
         self.tile = None
+        # CamPath state (include/synerfgine/cam_path.cuh:116-152): the camera follows the keyframe path while `is_playing`
+        self.is_playing = False
+        self.current_frame = 0
+        self.path_frames = 0          # 0 = the scene's total_time_ms * fps / 1000; bench.py resamples the path to 24 / 64 frames
+        self.enable_animations = False
 
     def set_virtual_world(self, config_fp, base_dir=None):
         self.scene = Scene.from_file(config_fp, base_dir)
         self.rt = self.scene.rt.copy()
+        self.is_playing = self.scene.move_on_start and self.scene.n_keyframes >= 2
+        self.enable_animations = self.scene.animations
 
     def set_virtual_world_json(self, json_text, base_dir=None):
         self.scene = Scene(json_text, base_dir)
         self.rt = self.scene.rt.copy()
+        self.is_playing = self.scene.move_on_start and self.scene.n_keyframes >= 2
+        self.enable_animations = self.scene.animations
 
     def init(self, res_width, res_height, testbed, tile=None):
         self.testbed, self.width, self.height, self.tile = testbed, res_width, res_height, tile
@@ -273,8 +282,32 @@ class Engine:
         sc.advance()
         tb._check(tb.lib.snb_update_scene(tb.ctx, sc.objects, sc.n_objects, sc.materials, sc.n_materials, sc.lights, sc.n_lights), "snb_update_scene")
 
+    def advance_camera_path(self):
+        """≙ CamPath::update -> advance_frame -> set_to_frame (cam_path.cuh:116-142), called by every Engine::frame (engine.cu:365):
+        the next frame of the keyframe path, wrapping to frame 0 past the last keyframe; moves the testbed's camera."""
+        sc, tb = self.scene, self.testbed
+        if not self.is_playing or sc.n_keyframes < 2:
+            return False
+        total = self.path_frames or sc.total_frames
+        between = max(1, total // max(sc.n_keyframes - 1, 1))
+        self.current_frame += 1
+        if self.current_frame // between + 1 >= sc.n_keyframes:
+            self.current_frame = 0
+        view, at, zoom = sc.camera_at(self.current_frame, total)
+        tb.set_camera_from_view(view, at, zoom)
+        tb._check(tb.lib.snb_reset_accumulation(tb.ctx), "snb_reset_accumulation")     # m_syn_camera_reset -> RayTracer::reset_accumulation (engine.cu:366-369)
+        return True
+
+    def step(self, **kw):
+        """One iteration of the reference's main loop, `while (engine.frame())` (src/main.cu:224): camera path, animations, render."""
+        self.advance_camera_path()
+        if self.enable_animations:
+            self.update_world_objects()
+        return self.frame(**kw)
+
     def frame(self, sync=True, host=False, tile=None):
-        """One Engine::frame. `tile` (an _lib.Tile) replaces the tile given to init() from this frame on."""
+        """Render with the current camera and world (Engine::frame from RayTracer::render on, engine.cu:374-406). `tile` (an _lib.Tile)
+        replaces the tile given to init() from this frame on. The per-frame camera-path / animation update is step()."""
         tb = self.testbed
         if tile is not None and (self.tile is None or (tile.x0, tile.y0, tile.w, tile.h) != (self.tile.x0, self.tile.y0, self.tile.w, self.tile.h)):
             self.tile = tile

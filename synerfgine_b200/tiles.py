@@ -205,3 +205,38 @@ def assemble_on_root(mine, bounds, rank, world, dist, frame=None):
     for r, p in enumerate(parts, start=1):
         frame[:, bounds[r]:bounds[r + 1]] = p
     return frame
+
+
+def assemble_rows_on_root(parts, bounds, rank, world, dist, frames):
+    """Row bands: every rank owns rows [bounds[r], bounds[r+1]) of the frame, which are CONTIGUOUS in a row-major frame, so each
+    buffer of a rank (rgba [h, W, 4], depth [h, W]: 20 B per pixel) travels as one exact-size point-to-point message
+    straight into its place in rank 0's frame — no .contiguous() copy on the sender, no staging tensor and no second copy on the
+    receiver. `parts`: this rank's owned rows of each buffer (contiguous views); `frames`: the full-size buffers on rank 0 (ignored
+    elsewhere). All messages of a frame go out in one grouped NCCL launch. Returns `frames` on rank 0, None elsewhere."""
+    if world == 1:
+        for f, p in zip(frames, parts):
+            if f.data_ptr() != p.data_ptr():
+                f[bounds[0]:bounds[1]].copy_(p)
+        return frames
+    for p in parts:
+        assert p.is_contiguous(), "row bands are contiguous: slice rows, not columns"
+    batched = dist.get_backend() == "nccl"
+    if rank != 0:
+        if batched:
+            for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, p, 0) for p in parts]):
+                req.wait()
+        else:
+            for p in parts:
+                dist.send(p, dst=0)
+        return None
+    views = [[f[bounds[r]:bounds[r + 1]] for f in frames] for r in range(world)]
+    if batched:
+        reqs = dist.batch_isend_irecv([dist.P2POp(dist.irecv, v, r) for r in range(1, world) for v in views[r]])
+    else:
+        reqs = [dist.irecv(v, src=r) for r in range(1, world) for v in views[r]]
+    for v, p in zip(views[0], parts):
+        if v.data_ptr() != p.data_ptr():
+            v.copy_(p)
+    for req in reqs:
+        req.wait()
+    return frames

@@ -8,24 +8,10 @@ from synerfgine_b200 import _lib
 from synerfgine_b200._lib import View
 from synerfgine_b200.synthetic import SyntheticModel
 
+from synerfgine_b200 import workloads
+from synerfgine_b200.workloads import camera_matrix, make_view, model  # noqa: F401  (the tests' names for the shared workload helpers)
+
 _models = {}
-
-
-def model(kind="fox16x2"):
-    """Cached synthetic models: the two encodings of SURVEY §0 plus the bounded (aabb 1) and unbounded (aabb 16) cases."""
-    if kind not in _models:
-        cfg = {
-            "fox16x2": dict(n_levels=16, n_feat=2, log2_T=19, aabb_scale=4),
-            "fox8x4": dict(n_levels=8, n_feat=4, log2_T=19, aabb_scale=4),
-            "small16x2": dict(n_levels=16, n_feat=2, log2_T=15, aabb_scale=4),
-            "unit16x2": dict(n_levels=16, n_feat=2, log2_T=15, aabb_scale=1),
-            "big16x2": dict(n_levels=16, n_feat=2, log2_T=16, aabb_scale=16),
-            "f1": dict(n_levels=32, n_feat=1, log2_T=14, aabb_scale=2),
-            "f8": dict(n_levels=4, n_feat=8, log2_T=14, aabb_scale=2),
-            "noocc": dict(n_levels=16, n_feat=2, log2_T=14, aabb_scale=1, occupancy=False, density_gain=12.0),
-        }[kind]
-        _models[kind] = SyntheticModel(**cfg)
-    return _models[kind]
 
 
 def cropped_model():
@@ -41,25 +27,6 @@ def cropped_model():
         m.render_aabb_min, m.render_aabb_max = [-0.2, -0.4, -0.3], [1.0, 0.75, 1.2]
         _models["cropped"] = m
     return _models["cropped"]
-
-
-def camera_matrix(view=(-0.30, -0.45, -0.84), at=(0.5, 0.42, 0.5), zoom=1.0):
-    lib = _lib.load()
-    out = np.zeros(12, np.float32)
-    v = np.asarray(view, np.float32); a = np.asarray(at, np.float32)
-    assert lib.snb_camera_from_view(v.ctypes.data_as(_lib.pf32), a.ctypes.data_as(_lib.pf32), float(zoom), out.ctypes.data_as(_lib.pf32)) == 0
-    return out
-
-
-def make_view(w, h, cam=None, spp=0, snap=1, fov=50.625):
-    v = View()
-    cam = camera_matrix() if cam is None else cam
-    v.camera[:] = [float(x) for x in cam]
-    f = float(np.float32(0.5 / math.tan(0.5 * fov * math.pi / 180.0)) * np.float32(h))
-    v.focal_length[:] = [f, f]
-    v.screen_center[:] = [0.5, 0.5]
-    v.width, v.height, v.spp, v.snap_to_pixel_centers = w, h, spp, snap
-    return v
 
 
 def psnr(a, b):
