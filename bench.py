@@ -383,7 +383,7 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize()
         launches0 = tb.launch_count()
         sampler = ClockSampler(local_rank); sampler.start()
-        step_ms, march_ms, stage_acc, samples, rays, march_stats, alt = [], [], {}, 0, 0, {}, None
+        step_ms, march_ms, stage_acc, samples, rays, march_stats, alt, pass_log = [], [], {}, 0, 0, {}, None, []
         for _ in range(K):
             flush.zero_()                                  # L2 flush between timed iterations (outside the event pair)
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
@@ -396,6 +396,7 @@ def run_ours(args, rank, local_rank, world):
             for k_, v_ in st.items():
                 stage_acc[k_] = stage_acc.get(k_, 0.0) + v_ / K
             c = tb.counters(); samples += c["samples"]; rays += c["rays"]
+            ast_ = (C.c_uint32 * 132)(); lib.snb_get_alt_status(ctx, ast_); pass_log.append((int(ast_[0]), int(ast_[1])))
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -405,7 +406,8 @@ def run_ours(args, rank, local_rank, world):
         march_stats["ws_pipeline"] = {k_: round(float(v_), 4) for k_, v_ in tb.ws_profile().items()}
         ast = (C.c_uint32 * 132)(); lib.snb_get_alt_status(ctx, ast)
         alt = {"passes_last_frame": int(ast[0]), "converged": int(ast[1]), "batch_lengths": [int(x) for x in ast[68:84]], "alive_rays_per_batch": [int(x) for x in ast[4:20]],
-               "external_checks": sched_checks}
+               "external_checks": sched_checks,
+               "march_passes_per_frame_mean": float(np.mean([p for p, _ in pass_log])) if pass_log else None, "frames_converged": int(sum(c_ for _, c_ in pass_log)), "frames": len(pass_log)}
         total_ms = torch.tensor([sum(step_ms)], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)     # device time, max over ranks
@@ -470,7 +472,7 @@ def run_ours(args, rank, local_rank, world):
             pm = float(np.mean(ms))
             present = {"kernel": "k_present", "ms": round(pm, 4), "bound": "hbm", "algorithmic_bytes": W * H * 19,
                        "achieved_gbs": round(W * H * 19 / (pm * 1e-3) / 1e9, 1), "note": "16 B in + 3 B out per pixel, L2 flushed before each launch"}
-    tb_march = (args.march or os.environ.get("SNB_MARCH") or "ws")
+    tb_march = (args.march or os.environ.get("SNB_MARCH") or "lane")
 
     if rank == 0:
         hbm, tflops, src = measured_peaks()

@@ -150,8 +150,8 @@ const char* snb_version(void);
  *   "alt_batch"    = "1".."8"        batch length of alt_schedule = fixed
  *   "alt_target_queries" = "2097152" target_n_queries of NerfTracer::trace_alt (src/testbed_nerf.cu:2188); tests lower it to exercise short batches on small frames
  * Implementation selectors (A/B measurements; frames are bit-identical unless noted):
- *   "march"      = "ws" (default: warp-specialised pipeline, MLPs on tcgen05 tensor cores with TMEM accumulators) | "lane" (one ray per
- *                  lane, warp-level mma.sync); same samples, outputs equal within fp32 summation order of the MLPs
+ *   "march"      = "lane" (default: one ray per lane, MLPs on warp-level mma.sync) | "ws" (warp-specialised pipeline, MLPs on tcgen05 tensor
+ *                  cores with TMEM accumulators; measured slower on C2); same samples, outputs equal within fp32 summation order
  *   "mlp"        = "mma" | "tc"   evaluator of the snb_network_inference parity tap (outputs equal within fp16 rounding)
  *   "overlap"    = "1" | "0"      mesh layer on a second stream
  *   "dead_terms" = "1" | "0"      skip NeRF shadow terms that no written pixel can observe (identical frame and RNG states)

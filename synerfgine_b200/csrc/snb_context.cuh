@@ -69,7 +69,7 @@ struct snb_ctx {
 	int fused_blocks_per_sm = 0;
 	int lane_blocks_per_sm[16] = {};   // resident CTAs per SM of each k_nerf_march_fused instance launched by THIS context (0 = not set up yet)
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
-	int march_variant = 6;             // 6 = warp-specialised tcgen05 pipeline (k_nerf_march_ws, snb_march_ws.cuh), 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused)
+	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused: the faster one, default), 6 = warp-specialised tcgen05 pipeline (k_nerf_march_ws)
 	bool ws_ready[8] = {};             // dynamic shared-memory opt-in done for each k_nerf_march_ws instance on this context's device
 	// batch schedule of the sng compositor (AltState in snb_nerf_kernels.cuh): 0 = "auto" (device-resident sequence, verified and
 	// repeated inside the frame), 1 = "external" (one pass; the caller reads the counts and sets the sequence: multi-GPU), 2 = "fixed"

@@ -1,5 +1,5 @@
 // synerfgine_b200 — the persistent NeRF march as a warp-specialised pipeline with both MLPs on the 5th-generation tensor cores
-// (tcgen05.mma, accumulators in TMEM, weights by one bulk-TMA copy): march option "ws", the default.
+// (tcgen05.mma, accumulators in TMEM, weights by one bulk-TMA copy): march option "ws".
 //
 // Same replacement set as k_nerf_march_fused (snb_nerf_kernels.cuh): generate_next_nerf_network_inputs, compact_kernel_nerf,
 // kernel_grid, kernel_sh, kernel_mlp_fused x2, extract_density, composite_kernel_nerf(_alt), extract_from_payload /

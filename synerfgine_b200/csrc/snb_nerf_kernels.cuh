@@ -63,7 +63,7 @@ SNB_HD uint32_t alt_steps_for(uint32_t target, uint32_t n_alive) {
 	return s < 1u ? 1u : (s > 8u ? 8u : s);
 }
 __global__ void k_alt_verify(AltState* st, uint32_t target, const unsigned int* __restrict__ queue_tail, uint32_t last_pass, uint32_t external) {
-	__shared__ uint32_t s_bad;
+	__shared__ uint32_t s_bad, s_used[kAltSched], s_n[kAltSched], s_want[kAltSched];
 	const int j = threadIdx.x;
 	if (j == 0) s_bad = 0xFFFFFFFFu;
 	__syncthreads();
@@ -72,15 +72,35 @@ __global__ void k_alt_verify(AltState* st, uint32_t target, const unsigned int* 
 	uint32_t used = st->sched[j];
 	if ((j == 0 && !external) || used == 0) used = alt_steps_for(target, *queue_tail);
 	const uint32_t want = n ? alt_steps_for(target, n) : 8u;
+	s_used[j] = used; s_n[j] = n; s_want[j] = want;
 	if (n && want != used) atomicMin(&s_bad, (uint32_t)j);
 	if (j == kAltSched - 1 && n > target / 8u) atomicMin(&s_bad, (uint32_t)kAltSched);   // still below 8 after the last tracked batch: inexact beyond
 	__syncthreads();
-	if (!external) st->sched[j] = (uint8_t)want;   // external: the counts of one tile say nothing about the frame; the caller sums them
-	if (j == 0) {
-		const bool ok = s_bad == 0xFFFFFFFFu;
-		st->passes += 1; st->converged = ok ? 1u : 0u; st->last_mismatch = s_bad;
-		st->redo = (!ok && !last_pass && s_bad < (uint32_t)kAltSched) ? 1u : 0u;
+	if (j != 0) return;
+	const uint32_t bad = s_bad;
+	const bool ok = bad == 0xFFFFFFFFu;
+	if (!external) {   // external: the counts of one tile say nothing about the frame; the caller sums them
+		// Entries up to the first mismatch are exact (n_alive_j depends on S_0..S_{j-1} only). Behind it the counts were taken under a
+		// sequence that is now known to be wrong, so the guess for the next pass is not want[j] but a replay: n_alive as a function of
+		// the samples composited so far (piecewise linear through the counts of this pass) is close to independent of how the samples
+		// are cut into batches, and walking it with the corrected lengths predicts where the later thresholds fall. The next
+		// pass is verified like this one; the replay only decides how many passes that takes.
+		uint32_t c = 0, k = 0, c_k = 0;               // samples composited at the start of batch i (new sequence) / batch k (this pass)
+		for (uint32_t i = 0; i < (uint32_t)kAltSched; ++i) {
+			uint32_t steps = s_want[i];
+			if (!ok && i > bad) {
+				while (k + 1 < (uint32_t)kAltSched && c_k + s_used[k] <= c) { c_k += s_used[k]; ++k; }
+				const uint32_t n0 = s_n[k], n1 = (k + 1 < (uint32_t)kAltSched) ? s_n[k + 1] : s_n[k];
+				const uint32_t frac_num = c > c_k ? c - c_k : 0u, frac_den = s_used[k] ? s_used[k] : 1u;
+				const uint32_t a = n0 - (uint32_t)(((unsigned long long)(n0 > n1 ? n0 - n1 : 0u) * (frac_num < frac_den ? frac_num : frac_den)) / frac_den);
+				steps = a ? alt_steps_for(target, a) : 8u;
+			}
+			st->sched[i] = (uint8_t)steps;
+			c += steps;
+		}
 	}
+	st->passes += 1; st->converged = ok ? 1u : 0u; st->last_mismatch = bad;
+	st->redo = (!ok && !last_pass && bad < (uint32_t)kAltSched) ? 1u : 0u;
 }
 // Start of a march pass: the first pass always runs and resets the per-frame state; later passes run only after a mismatch and
 // first undo what the previous pass wrote (tile buffers are cleared like ray generation clears them).

@@ -78,7 +78,7 @@ static int launch_fused_f(snb_ctx* c, const DevView& dv, const NerfOut& out, int
 // sng path: the batch lengths of the reference's lock-step march (AltState, snb_nerf_kernels.cuh) are carried on the device from
 // frame to frame; a pass whose own ray counts contradict the lengths it used is repeated (at most kAltPasses passes, each later
 // one a conditional launch that returns at once when the previous pass verified) — all enqueued without a host round trip.
-static const int kAltPasses = 3;
+static const int kAltPasses = 4;
 static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render_mode, float* fb, float* depth, float* positions) {
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	const int n_px = dv.tw * dv.th;

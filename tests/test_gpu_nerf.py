@@ -35,7 +35,7 @@ def dev(shape, dtype):
     return torch.zeros(shape, dtype=dtype, device="cuda")
 
 
-MARCHES = ["ws", "lane"]   # march kernels selectable with snb_set_option(ctx, "march", ...); the first one is the default
+MARCHES = ["lane", "ws"]   # march kernels selectable with snb_set_option(ctx, "march", ...); the first one is the default
 
 
 @pytest.mark.parametrize("kind,w,h,spp,snap", [("small16x2", 96, 64, 0, 1), ("small16x2", 64, 48, 3, 0), ("unit16x2", 64, 64, 0, 1), ("big16x2", 64, 64, 1, 0),
