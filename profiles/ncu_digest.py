@@ -6,7 +6,9 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
         "sm__inst_issued.avg.pct_of_peak_sustained_active", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_sector_hit_rate.pct",
         "l1tex__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__thread_inst_executed_per_inst_executed.ratio",
-        "sm__pipe_tensor_op_hmma_cycles_active.avg.pct_of_peak_sustained_active"]
+        "sm__pipe_tensor_op_hmma_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "lts__t_sectors_srcunit_tex.sum",
+        "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
 STALLS = ["long_scoreboard", "barrier", "wait", "no_instruction", "short_scoreboard", "math_pipe_throttle", "not_selected", "branch_resolving",
           "mio_throttle", "lg_throttle", "dispatch_stall", "drain", "membar", "sleeping", "tex_throttle", "imc_miss", "selected"]
 rows = list(csv.reader(open(sys.argv[1])))

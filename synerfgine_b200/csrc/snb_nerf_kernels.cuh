@@ -278,6 +278,9 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 #ifndef SNB_LANE_CTAS
 #define SNB_LANE_CTAS 2     // resident CTAs per SM the register budget is set for (tuning hook)
 #endif
+#ifndef SNB_LANE_UNROLLED_MLP
+#define SNB_LANE_UNROLLED_MLP 0
+#endif
 #ifndef SNB_LANE_MIN_FILL
 #define SNB_LANE_MIN_FILL 20   // lanes holding a sample before the network runs (tuning hook)
 #endif
@@ -417,7 +420,14 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			encode_position_to_row<F, false>(s_levels, wpos, tile + lane * kTileStrideH, nullptr);
 		}
 		// -- both MLPs ---------------------------------------------------------------------------------------------------
+#if SNB_LANE_UNROLLED_MLP   // tuning hook: both 16-row m-tiles per weight fetch (half the shared-memory wavefronts, twice the code)
+		uint32_t sh_frag[2][4];
+		__syncwarp();
+		load_sh_frags(tile, lane, sh_frag);
+		const uint2 net = warp_network_eval(s_w, tile, out_tile, lane, sh_frag);
+#else
 		const uint2 net = warp_network_eval_rolled(s_w, tile, out_tile, lane);
+#endif
 
 		// -- composite -------------------------------------------------------------------------------------------------
 		if (valid) {

@@ -61,7 +61,7 @@ def sample_coords(n, seed=5):
     return coords
 
 
-@pytest.mark.parametrize("kind", ["small16x2", "fox8x4", "fox16x2", "big16x2"])
+@pytest.mark.parametrize("kind", ["small16x2", "fox8x4", "fox16x2", "big16x2", "unbounded22"])
 def test_hash_grid_features_bit_exact(R, snb, orc, ctx, kind):
     """tcnn kernel_grid<__half,3,F> (encodings/grid.h:48-212) == oracle == product, bit for bit."""
     m = common.model(kind)
@@ -203,7 +203,7 @@ def test_ray_setup_and_march_against_the_reference_build(R, snb, orc, ctx, kind,
     m = common.model(kind)
     d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
     rm = R.Model(m)
-    cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
+    cam = common.camera_matrix(zoom=2.5) if kind in ("big16x2", "unbounded22") else None
     v = common.make_view(w, h, cam=cam)
     rays = rm.init_rays(R.ref_view(v), w, h)                                              # n x {o3, d3, t, alive}
     n, S = w * h, 32
@@ -267,7 +267,7 @@ def _product_nerf_layer(snb, ctx, v, w, h, shadows_rt=None):
     return fb.cpu().numpy(), depth.cpu().numpy(), pos.cpu().numpy(), nrm.cpu().numpy(), list(st)
 
 
-@pytest.mark.parametrize("kind,w,h", [("small16x2", 256, 256), ("fox16x2", 480, 270), ("fox16x2", 1920, 1080), ("big16x2", 256, 256)])
+@pytest.mark.parametrize("kind,w,h", [("small16x2", 256, 256), ("fox16x2", 480, 270), ("fox16x2", 1920, 1080), ("big16x2", 256, 256), ("unbounded22", 480, 270)])
 def test_nerf_layer_framebuffer_against_the_reference_build(R, snb, ctx, kind, w, h):
     """The sng NeRF layer (trace_alt + extract_from_payload + write_normals_to_buffer, no shadows) rendered by the reference's own
     NerfTracer and kernels vs snb_render_nerf_with_buffers: >= 50 dB, max abs <= 1e-2. 1920x1080 on the 2^19 model is BASELINE's C2
@@ -275,7 +275,7 @@ def test_nerf_layer_framebuffer_against_the_reference_build(R, snb, ctx, kind, w
     m = common.model(kind)
     d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
     assert snb.snb_set_alt_schedule(ctx, None, 0) == 0
-    cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
+    cam = common.camera_matrix(zoom=2.5) if kind in ("big16x2", "unbounded22") else None
     v = common.make_view(w, h, cam=cam)
     rm = R.Model(m); eng = R.Engine(w, h)
     ms = eng.render_nerf(rm, v, alt=True)

@@ -149,12 +149,55 @@ def test_syn_layer_lens0_matches_oracle(snb, orc, ctx):
     assert common.psnr(out, ref["final"]) > 45
 
 
-@pytest.mark.parametrize("name,w,h", [("c2", 96, 64), ("c3", 64, 48)])
+@pytest.mark.parametrize("name,w,h", [("c2", 96, 64), ("c3", 64, 48), ("c2", 240, 135)])
 def test_full_frame_matches_oracle(snb, orc, ctx, name, w, h):
+    """north_star's bar on the whole frame: >= 50 dB and max abs <= 1e-2 on every pixel except a COUNTED, capped set. Those are
+    pixels where a hard decision (a shadow ray just reaching / just missing a triangle or an occupied cell, a mesh silhouette)
+    falls the other way because libm (oracle) and CUDA (product) round a transcendental differently: they must be few (<= 1 %),
+    and they must sit on mesh pixels, shadow-receiving NeRF pixels or their direct neighbours — printed for inspection."""
     out, od, ref, sc, rt, v = frame_pair(snb, ctx, name, w, h)
     assert (ref["syn_depth"] < 1000).mean() > 0.02 and (ref["nerf_rgba"][..., 3] > 0.5).mean() > 0.1
-    assert close_fraction(out, ref["final"], 1e-2) > 0.99, close_fraction(out, ref["final"], 1e-2)
+    both_nan = np.isnan(out) & np.isnan(ref["final"])
+    d = np.where(both_nan, 0.0, np.abs(out - ref["final"])); d = np.where(np.isnan(d), np.inf, d)
+    bad = d.max(-1) > 1e-2
+    n_bad = int(bad.sum())
+    ys, xs = np.nonzero(bad)
+    on_mesh = ref["syn_depth"] < 1000
+    shadowed = ref["shadow"] < 0.999
+    near = np.zeros_like(bad)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            near |= np.roll(np.roll(on_mesh | shadowed, dy, 0), dx, 1)
+    print(f"[{name} {w}x{h}] pixels over 1e-2: {n_bad} of {w * h} ({100.0 * n_bad / (w * h):.3f} %), on mesh {int((bad & on_mesh).sum())}, on shadowed NeRF {int((bad & shadowed & ~on_mesh).sum())}; first: {list(zip(xs[:8].tolist(), ys[:8].tolist()))}")
+    assert n_bad <= 0.01 * w * h, n_bad
+    assert int((bad & ~near).sum()) <= max(2, n_bad // 10), "out-of-tolerance pixels away from any mesh / shadow edge"
+    ok = ~bad & np.isfinite(out).all(-1) & np.isfinite(ref["final"]).all(-1)
+    assert common.psnr(out[ok], ref["final"][ok]) >= 50.0, common.psnr(out[ok], ref["final"][ok])
     assert finite_psnr(out, ref["final"]) > 40, finite_psnr(out, ref["final"])
+
+
+def test_overlay_with_two_resolutions_matches_oracle(snb, orc, ctx):
+    """overlay_nerf with syn_px_scale = 2 (the reference's two-resolution mode, src/synerfgine/raytracer.cu:242-246: the NeRF layer at
+    half the mesh layer's resolution, nearest-neighbour lookup nc = sc / scale) against the oracle's restatement."""
+    rng = np.random.default_rng(21)
+    sw, sh, scale = 64, 48, 2
+    nw, nh = sw // scale, sh // scale
+    syn = rng.random((sh, sw, 4)).astype(np.float32); sdepth = (rng.random((sh, sw)) * 3).astype(np.float32)
+    sdepth[rng.random((sh, sw)) < 0.5] = 16384.0                                    # pixels the mesh layer did not hit
+    nerf = rng.random((nh, nw, 4)).astype(np.float32); ndepth = (rng.random((nh, nw)) * 3).astype(np.float32)
+    for curve in (0, 1):
+        rt = common.default_rt(syn_px_scale=scale, exposure=0.5, tonemap_curve=curve, depth_offset=0.1)
+        d_syn, d_sd, d_n, d_nd = (torch.from_numpy(a).cuda() for a in (syn, sdepth, nerf, ndepth))
+        out, od = dev((sh, sw, 4)), dev((sh, sw))
+        rc = snb.snb_overlay(ctx, sw, sh, C.byref(rt), d_syn.data_ptr(), d_sd.data_ptr(), d_n.data_ptr(), d_nd.data_ptr(), out.data_ptr(), od.data_ptr())
+        assert rc == 0 and snb.snb_sync(ctx) == 0, snb.snb_last_error(ctx)
+        ref = np.zeros((sh, sw, 4), np.float32); rdepth = np.zeros((sh, sw), np.float32)
+        orc.orc_overlay(sw, sh, scale, O.P(syn), O.P(sdepth), O.P(nerf), O.P(ndepth), 1, 1, curve, 0.5, 0.1, O.P(ref), O.P(rdepth))
+        np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=3e-5, atol=3e-6)
+        np.testing.assert_array_equal(od.cpu().numpy(), rdepth)
+    # which layer wins must follow the coarse NeRF pixel: a 2 x 2 block of mesh pixels shares one NeRF depth
+    picks_nerf = ~((sdepth - 0.1) < np.repeat(np.repeat(ndepth, scale, 0), scale, 1))
+    assert 0.2 < picks_nerf.mean() < 0.9
 
 
 def test_temporal_blend_two_frames(snb, orc, ctx):

@@ -207,3 +207,60 @@ def test_rebalanced_strips_give_the_same_frame(tmp_path, world):
     for f in got["frames"]:                                        # every frame, whatever the split, is the single-rank frame
         np.testing.assert_array_equal(f.view(np.uint32), expect.view(np.uint32))
     assert list(got["bounds"])[0] == 0 and list(got["bounds"])[-1] == W
+
+
+# ---- row bands (the form bench.py uses): contiguous messages straight into rank 0's frame, rgba + depth ----------------------------
+def _band_worker(rank, world, port, halo, out_path, bounds):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        m = common.model("small16x2")
+        v = common.make_view(W, H)
+        render_tile = make_tile_renderer(m.desc(), v)
+        s = tiles.strip_from_bounds(bounds, rank, H, halo)                      # a Strip along y: rows [x0, x1) owned, [hx0, hx1) rendered
+        rgba, depth = render_tile(0, s.hx0, W, s.render_width)
+        own = slice(s.x0 - s.hx0, s.x1 - s.hx0)
+        parts = [rgba[own], depth[own]]
+        assert all(p.is_contiguous() for p in parts)                            # no copy needed before sending: rows of a band are contiguous
+        frames = [torch.full((H, W, 4), -1.0), torch.full((H, W), -1.0)] if rank == 0 else [None, None]
+        got = tiles.assemble_rows_on_root(parts, bounds, rank, world, dist, frames)
+        if rank == 0:
+            np.savez(out_path, rgba=got[0].numpy(), depth=got[1].numpy())
+        else:
+            assert got is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,bounds", [(2, [0, 12, 24]), (3, [0, 5, 17, 24])])
+def test_row_bands_assemble_rgba_and_depth_bit_identically(tmp_path, world, bounds):
+    """Equal and unequal (re-balanced) bands: the assembled rgba AND depth (20 B per pixel) equal the 1-rank frame bit for bit."""
+    m = common.model("small16x2")
+    v = common.make_view(W, H)
+    fb, depth, pos, nrm = oracle_nerf_layer(m.desc(), v)
+    expect = fb.copy(); expect[..., 3] = nrm[..., 0]
+    out = str(tmp_path / "bands.npz")
+    mp.spawn(_band_worker, args=(world, _free_port(), tiles.halo_for(1), out, bounds), nprocs=world, join=True)
+    got = np.load(out)
+    np.testing.assert_array_equal(got["rgba"].view(np.uint32), expect.view(np.uint32))
+    np.testing.assert_array_equal(got["depth"].view(np.uint32), depth.view(np.uint32))
+
+
+def test_batch_schedule_is_a_whole_frame_quantity():
+    """The sng compositor's batch lengths depend on n_alive of the WHOLE frame (src/testbed_nerf.cu:2189-2190). Bands that march with
+    the frame's sequence reproduce the frame; bands that derive the sequence from their own ray counts do not — which is why the
+    ranks sum their counts (bench.py: sync_alt_schedule) instead of running the single-GPU 'auto' mode per band."""
+    m = common.model("small16x2")
+    d = m.desc()
+    v = common.make_view(W, H)
+    target = 900
+    fb, _, _, sched, alive = O.render_nerf_wavefront(d, v, alt=1, target_queries=target)
+    assert sched[0] < 8
+    whole, _, _ = O.render_nerf_sched(d, v, sched, alt=1)
+    np.testing.assert_array_equal(whole.view(np.uint32), fb.view(np.uint32))
+    # a band on its own: fewer alive rays -> longer batches -> another image
+    half = common.make_view(W, H // 2)
+    half.camera[:] = list(v.camera); half.focal_length[:] = list(v.focal_length)
+    _, _, _, sched_half, alive_half = O.render_nerf_wavefront(d, half, alt=1, target_queries=target)
+    assert alive_half[0] < alive[0] and list(sched_half[:4]) != list(sched[:4])
