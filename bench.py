@@ -310,7 +310,7 @@ def run_ours(args, rank, local_rank, world):
         used = list(st[68:132])
         sched_checks["n"] += 1
         if [u if u else want[0] for u in used] != want:
-            sched_checks["changed"] += 1
+            sched_checks["changed"] += 1                   # the frame just rendered used a sequence the whole-frame counts contradict
         arr = (C.c_uint8 * 64)(*want)
         assert lib.snb_set_alt_schedule(ctx, arr, 64) == 0
 
@@ -407,7 +407,8 @@ def run_ours(args, rank, local_rank, world):
         ast = (C.c_uint32 * 132)(); lib.snb_get_alt_status(ctx, ast)
         alt = {"passes_last_frame": int(ast[0]), "converged": int(ast[1]), "batch_lengths": [int(x) for x in ast[68:84]], "alive_rays_per_batch": [int(x) for x in ast[4:20]],
                "external_checks": sched_checks,
-               "march_passes_per_frame_mean": float(np.mean([p for p, _ in pass_log])) if pass_log else None, "frames_converged": int(sum(c_ for _, c_ in pass_log)), "frames": len(pass_log)}
+               "march_passes_per_frame_mean": float(np.mean([p for p, _ in pass_log])) if pass_log else None, "frames_converged": (int(sum(c_ for _, c_ in pass_log)) if not (split_frame and not args.alt_schedule) else None), "frames": len(pass_log),
+               "note": ("row bands: every band marches with the WHOLE frame's batch lengths; the ranks sum their counts on the balancer's cadence and 'changed' counts the checks that found the sequence stale (0 = every checked frame exact)" if split_frame else None)}
         total_ms = torch.tensor([sum(step_ms)], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)     # device time, max over ranks

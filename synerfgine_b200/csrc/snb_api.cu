@@ -246,7 +246,9 @@ static int upload_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_o
 	if (n_objects) SNB_CUDA(c, cudaMemcpyAsync(c->d_objects.p, ho.data(), n_objects * sizeof(DevObject), cudaMemcpyHostToDevice, c->stream));
 	if (n_materials) SNB_CUDA(c, cudaMemcpyAsync(c->d_materials.p, hm.data(), n_materials * sizeof(DevMaterial), cudaMemcpyHostToDevice, c->stream));
 	if (n_lights) SNB_CUDA(c, cudaMemcpyAsync(c->d_lights.p, hl.data(), n_lights * sizeof(DevLight), cudaMemcpyHostToDevice, c->stream));
-	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	// No stream synchronisation: copies from pageable host memory return once the source has been staged, and they are ordered on the
+	// context's stream behind the previous frame (whose mesh layer on the second stream was joined before its overlay), so a per-frame
+	// snb_update_scene (animated objects, Engine::update_world_objects) does not drain the GPU.
 	c->scene.objects = c->d_objects.as<DevObject>(); c->scene.n_objects = n_objects;
 	c->scene.materials = c->d_materials.as<DevMaterial>(); c->scene.n_materials = n_materials;
 	c->scene.lights = c->d_lights.as<DevLight>(); c->scene.n_lights = n_lights;
