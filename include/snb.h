@@ -62,6 +62,23 @@ typedef struct {
 	int32_t snap_to_pixel_centers;
 } snb_view;
 
+/* The rest of the stock render's camera model: the arguments Testbed::render_nerf passes to NerfTracer::init_rays_from_camera beyond the
+ * pinhole camera (src/testbed_nerf.cu:2679-2740 -> init_rays_with_payload_kernel_nerf :1855-1970 -> uv_to_ray,
+ * include/neural-graphics-primitives/common_device.cuh:403-470). Applies to snb_render_nerf (and the snb_march_trace tap) only: the
+ * sng path's ray generation takes none of them (src/synerfgine/raytracer.cu:59-98). Foveation, hidden-area mask and the learned
+ * distortion grid are VR / training features and stay out (SURVEY.md 8 "out of scope"). */
+enum { SNB_LENS_PERSPECTIVE = 0, SNB_LENS_OPENCV = 1, SNB_LENS_FTHETA = 2, SNB_LENS_LATLONG = 3, SNB_LENS_OPENCV_FISHEYE = 4, SNB_LENS_EQUIRECTANGULAR = 5 }; /* ELensMode, common.h:118-126 */
+typedef struct {
+	float camera1[12];           /* camera at the end of the shutter interval (column-major 4x3); snb_view.camera is camera0 */
+	float rolling_shutter[4];    /* pixel time = a + b*u + c*v + d*motionblur_time; the windowless render passes {0,0,0,1} */
+	float parallax_shift[3];     /* m_parallax_shift */
+	float near_distance;         /* m_render_near_distance */
+	float plane_z;               /* m_slice_plane_z + m_scale: focus distance; negative = slice plane (rays die, depth = -plane_z) */
+	float aperture_size;         /* m_aperture_size: 0 = pinhole */
+	int32_t lens_mode;           /* SNB_LENS_* (m_nerf.render_lens.mode when render_with_lens_distortion) */
+	float lens_params[7];        /* Lens::params */
+} snb_camera_ex;
+
 /* Pixel tile of a view rendered by this context (multi-GPU sharding). Pixel indices used for
  * sampling stay global. A zero-sized tile means the whole view. */
 typedef struct { int32_t x0, y0, w, h; } snb_tile;
@@ -194,6 +211,11 @@ int snb_reset_accumulation(snb_ctx* ctx);
 /* ---- the hot path ------------------------------------------------------------------------------------- */
 /* ≙ Testbed::render_nerf (testbed.h:358-371; src/testbed_nerf.cu:2679-2837): stock NeRF frame into fb/depth. */
 int snb_render_nerf(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, int render_mode, float* fb_rgba_dev, float* depth_dev);
+/* Extended camera of the following snb_render_nerf calls (NULL: back to the pinhole path, bit-identical to never having called this). */
+int snb_set_camera_ex(snb_ctx* ctx, const snb_camera_ex* ex);
+/* ≙ Testbed::m_envmap's inference view (include/neural-graphics-primitives/envmap.cuh:24-50): w x h RGBA fp32 host texels, row-major;
+ * background of every valid primary ray of snb_render_nerf, composited under the NeRF colour. NULL or w*h == 0 removes it. */
+int snb_set_envmap(snb_ctx* ctx, const float* rgba_host, int32_t w, int32_t h);
 /* ≙ RayTracer::render (raytracer.cuh:116-128; src/synerfgine/raytracer.cu:312-370): mesh layer into the
  * context's syn buffers; optional copies out. */
 int snb_render_syn(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* syn_rgba_dev, float* syn_depth_dev);
@@ -261,6 +283,9 @@ int snb_scene_path_info(const snb_scene* s, uint32_t* total_frames, int32_t* pla
 /* ≙ Testbed::reset_camera + set_view_dir + set_look_at + set_scale (src/testbed.cu:405-425,470-492) as Engine::init
  * applies the JSON camera block (engine.cu:148-151): camera matrix (mat4x3, column-major) out. */
 int snb_camera_from_view(const float* view3, const float* at3, float zoom, float* out12);
+/* ≙ camera_log_lerp (include/neural-graphics-primitives/common_device.cuh:658-660): exp(log(b * a^-1) * t) * a, the end-of-shutter
+ * camera of a motion-blur sample (src/python_api.cu:157-189). Matrices are mat4x3 column-major. */
+int snb_camera_log_lerp(const float* a12, const float* b12, float t, float* out12);
 /* ≙ VirtualObject::next_frame / Light::next_frame (virtual_object.cuh:53-64; light.cuh:40-49). */
 int snb_scene_advance(snb_scene* s);
 /* ≙ TriangleBvhWithBranchingFactor<2>::build (src/triangle_bvh.cu:615-718); reorders tris in place. */

@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
 // Ray generation, start jitter and the occupancy-cascade DDA march.
 #include "march.h"
+#include <vector>
 
 namespace orc {
 
@@ -322,26 +323,170 @@ Ray uv_to_ray_pinhole(vec2 uv, ivec2 resolution, vec2 focal_length, const mat4x3
 	return {origin, dir};
 }
 
-// testbed_nerf.cu:1855-1970 (init_rays_with_payload_kernel_nerf), pinhole / no envmap / plane_z >= 0.
+// ---- the general camera model (installed by orc_set_camera_ex / orc_set_envmap) -------------------------------------------------------
+bool g_has_camera_ex = false;
+orc_camera_ex g_camera_ex;
+static std::vector<float> g_envmap; static int g_env_w = 0, g_env_h = 0;
+
+// common_device.cuh:361-368
+static mat4x3 xform_given_rolling_shutter2(const mat4x3& start, const mat4x3& end, const float* rs, vec2 uv, float motionblur_time) {
+	float pixel_t = rs[0] + rs[1] * uv.x + rs[2] * uv.y + rs[3] * motionblur_time;
+	vec3 pos = start.c[3] + (end.c[3] - start.c[3]) * pixel_t;
+	mat3 rot = quat_to_mat3(qnormalize(qslerp(quat_from_mat3(to_mat3(start)), quat_from_mat3(to_mat3(end)), pixel_t)));
+	return {{rot.c[0], rot.c[1], rot.c[2], pos}};
+}
+// common_device.cuh:249-288
+static void opencv_delta(const float* p, float u, float v, float* du, float* dv) {
+	const float k1 = p[0], k2 = p[1], p1 = p[2], p2 = p[3];
+	const float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+	const float radial = k1 * r2 + k2 * r2 * r2;
+	*du = u * radial + 2.0f * p1 * uv + p2 * (r2 + 2.0f * u2);
+	*dv = v * radial + 2.0f * p2 * uv + p1 * (r2 + 2.0f * v2);
+}
+static void fisheye_delta(const float* p, float u, float v, float* du, float* dv) {
+	const float r = std::sqrt(u * u + v * v);
+	if (r > (float)std::numeric_limits<double>::epsilon()) {
+		const float theta = std::atan(r), theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+		const float thetad = theta * (1.0f + p[0] * theta2 + p[1] * theta4 + p[2] * theta6 + p[3] * theta8);
+		*du = u * thetad / r - u; *dv = v * thetad / r - v;
+	} else { *du = 0.0f; *dv = 0.0f; }
+}
+// common_device.cuh:290-329
+template <typename F> static void iterative_undistortion(const float* params, float* u, float* v, F fun) {
+	const float eps = std::numeric_limits<float>::epsilon();
+	const float x0[2] = {*u, *v};
+	float x[2] = {*u, *v};
+	for (uint32_t i = 0; i < 100; ++i) {
+		const float step0 = std::max(eps, std::fabs(1e-6f * x[0])), step1 = std::max(eps, std::fabs(1e-6f * x[1]));
+		float dx[2], b0[2], f0[2], b1[2], f1[2];
+		fun(params, x[0], x[1], &dx[0], &dx[1]);
+		fun(params, x[0] - step0, x[1], &b0[0], &b0[1]); fun(params, x[0] + step0, x[1], &f0[0], &f0[1]);
+		fun(params, x[0], x[1] - step1, &b1[0], &b1[1]); fun(params, x[0], x[1] + step1, &f1[0], &f1[1]);
+		// J[col][row]
+		const float J00 = 1 + (f0[0] - b0[0]) / (2 * step0), J10 = (f1[0] - b1[0]) / (2 * step1), J01 = (f0[1] - b0[1]) / (2 * step0), J11 = 1 + (f1[1] - b1[1]) / (2 * step1);
+		const float rx = x[0] + dx[0] - x0[0], ry = x[1] + dx[1] - x0[1];
+		const float det = J00 * J11 - J10 * J01;
+		const float sx = (J11 * rx - J10 * ry) / det, sy = (-J01 * rx + J00 * ry) / det;
+		x[0] -= sx; x[1] -= sy;
+		if (sx * sx + sy * sy < 1e-10f) break;
+	}
+	*u = x[0]; *v = x[1];
+}
+// random_val.cuh:112-128
+static vec2 square2disk_shirley(vec2 sq) {
+	const float pi = 3.14159265358979323846f;
+	float phi, r;
+	const float a = sq.x, b = sq.y;
+	if (a * a > b * b) { r = a; phi = (pi / 4.0f) * (b / a); } else { r = b; phi = (pi / 2.0f) - (pi / 4.0f) * (a / b); }
+	return {r * std::cos(phi), r * std::sin(phi)};
+}
+// common_device.cuh:403-470 without foveation / hidden-area mask / distortion grid. Returns false for Ray::invalid().
+static bool uv_to_ray_general(uint32_t spp, vec2 uv, ivec2 resolution, vec2 focal_length, const mat4x3& camera, vec2 screen_center,
+                              const orc_camera_ex& ex, float aperture_size, Ray& out) {
+	const float pi = 3.14159265358979323846f;
+	vec3 dir;
+	if (ex.lens_mode == 2) {          // f_theta_undistortion, :370-383
+		const float xpix = (uv.x - screen_center.x) * ex.lens_params[5], ypix = (uv.y - screen_center.y) * ex.lens_params[6];
+		const float norm = std::sqrt(xpix * xpix + ypix * ypix);
+		const float* q = ex.lens_params;
+		const float alpha = q[0] + norm * (q[1] + norm * (q[2] + norm * (q[3] + norm * q[4])));
+		float sin_alpha = std::sin(alpha); const float cos_alpha = std::cos(alpha);
+		if (cos_alpha <= std::numeric_limits<float>::min() || norm == 0.0f) return false;
+		sin_alpha *= 1.0f / norm;
+		dir = {sin_alpha * xpix, sin_alpha * ypix, cos_alpha};
+		if (dir.x == 0.0f && dir.y == 0.0f && dir.z == 0.0f) return false;
+	} else if (ex.lens_mode == 3) {   // latlong_to_dir, :385-392
+		const float theta = (uv.y - 0.5f) * pi, phi = (uv.x - 0.5f) * pi * 2.0f;
+		dir = {std::sin(phi) * std::cos(theta), std::sin(theta), std::cos(phi) * std::cos(theta)};
+	} else if (ex.lens_mode == 5) {   // equirectangular_to_dir, :394-401
+		const float ct = (uv.y - 0.5f) * 2.0f, st = std::sqrt(std::max(1.0f - ct * ct, 0.0f)), phi = (uv.x - 0.5f) * pi * 2.0f;
+		dir = {std::sin(phi) * st, ct, std::cos(phi) * st};
+	} else {
+		dir = {(uv.x - screen_center.x) * (float)resolution.x / focal_length.x, (uv.y - screen_center.y) * (float)resolution.y / focal_length.y, 1.0f};
+		if (ex.lens_mode == 1) iterative_undistortion(ex.lens_params, &dir.x, &dir.y, opencv_delta);
+		else if (ex.lens_mode == 4) iterative_undistortion(ex.lens_params, &dir.x, &dir.y, fisheye_delta);
+	}
+	vec3 head_pos = {ex.parallax_shift[0], ex.parallax_shift[1], 0.0f};
+	dir -= head_pos * ex.parallax_shift[2];
+	dir = to_mat3(camera) * dir;
+	vec3 origin = to_mat3(camera) * head_pos + camera.c[3];
+	if (aperture_size != 0.0f) {
+		vec3 lookat = origin + dir * ex.plane_z;
+		const int px = (int)(uv.x * (float)resolution.x), py = (int)(uv.y * (float)resolution.y);
+		vec2 r2 = ld_random_val_2d(spp, (uint32_t)px * 19349663u + (uint32_t)py * 96925573u);
+		vec2 disk = square2disk_shirley({r2.x * 2.0f - 1.0f, r2.y * 2.0f - 1.0f});
+		vec2 blur = {aperture_size * disk.x, aperture_size * disk.y};
+		origin += camera.c[0] * blur.x + camera.c[1] * blur.y;
+		dir = (lookat - origin) / ex.plane_z;
+	}
+	origin += dir * ex.near_distance;
+	out = {origin, dir};
+	return true;
+}
+// envmap.cuh:24-50
+static vec4 read_envmap(vec3 dir) {
+	const float pi = 3.14159265358979323846f;
+	vec3 d = {dir.z, -dir.x, dir.y};
+	const float theta = std::acos(std::fmin(std::fmax(d.z, -1.0f), 1.0f)), phi = std::atan2(d.y, d.x);
+	const float cx = theta / pi, cy = phi / (2.0f * pi) + 0.5f;
+	const float fx = cy * (float)(g_env_w - 1), fy = cx * (float)(g_env_h - 1);
+	const int tx = (int)fx, ty = (int)fy;
+	const float wx = fx - (float)tx, wy = fy - (float)ty;
+	auto rd = [&](int x, int y) {
+		if (x < 0) x += g_env_w; else if (x >= g_env_w) x -= g_env_w;
+		y = std::max(std::min(y, g_env_h - 1), 0);
+		const float* t = g_envmap.data() + ((size_t)y * g_env_w + x) * 4;
+		return vec4{t[0], t[1], t[2], t[3]};
+	};
+	const vec4 a = rd(tx, ty), b = rd(tx + 1, ty), c = rd(tx, ty + 1), e = rd(tx + 1, ty + 1);
+	const float w00 = (1 - wx) * (1 - wy), w10 = wx * (1 - wy), w01 = (1 - wx) * wy, w11 = wx * wy;
+	return {((w00 * a.x + w10 * b.x) + w01 * c.x) + w11 * e.x, ((w00 * a.y + w10 * b.y) + w01 * c.y) + w11 * e.y,
+	        ((w00 * a.z + w10 * b.z) + w01 * c.z) + w11 * e.z, ((w00 * a.w + w10 * b.w) + w01 * c.w) + w11 * e.w};
+}
+
+// testbed_nerf.cu:1855-1970 (init_rays_with_payload_kernel_nerf). payload.n_steps carries 0; payload.t = 0 marks an invalid ray.
 void init_ray_payload(uint32_t x, uint32_t y, const orc_view& view, const MarchEnv& env, NerfPayload& payload) {
 	ivec2 res = {view.width, view.height};
 	uint32_t idx = x + res.x * y;
 	vec2 off = ld_random_pixel_offset(view.snap_to_pixel_centers ? 0 : view.spp);
 	vec2 uv = {((float)x + off.x) / (float)res.x, ((float)y + off.y) / (float)res.y};
 	mat4x3 cam0 = load_camera(view.camera);
-	mat4x3 camera = xform_given_rolling_shutter(cam0, ld_random_val(view.spp, idx * 72239731u), uv);
-	Ray ray = uv_to_ray_pinhole(uv, res, {view.focal_length[0], view.focal_length[1]}, camera, {view.screen_center[0], view.screen_center[1]});
+	Ray ray;
+	bool valid = true;
+	if (!g_has_camera_ex) {
+		mat4x3 camera = xform_given_rolling_shutter(cam0, ld_random_val(view.spp, idx * 72239731u), uv);
+		ray = uv_to_ray_pinhole(uv, res, {view.focal_length[0], view.focal_length[1]}, camera, {view.screen_center[0], view.screen_center[1]});
+	} else {
+		const orc_camera_ex& ex = g_camera_ex;
+		float aperture = ex.plane_z < 0.0f ? 0.0f : ex.aperture_size;
+		mat4x3 camera = xform_given_rolling_shutter2(cam0, load_camera(ex.camera1), ex.rolling_shutter, uv, ld_random_val(view.spp, idx * 72239731u));
+		valid = uv_to_ray_general(view.spp, uv, res, {view.focal_length[0], view.focal_length[1]}, camera, {view.screen_center[0], view.screen_center[1]}, ex, aperture, ray);
+	}
 	payload.max_weight = 0.0f;
 	payload.idx = idx; // (the reference leaves idx stale for dead rays; they are never read)
 	payload.n_steps = 0;
+	if (!valid) { payload.origin = {0, 0, 0}; payload.dir = {0, 0, 0}; payload.t = 0.0f; payload.alive = false; return; }
 	ray.d = normalize(ray.d);
 	float t = std::fmax(env.render_aabb.ray_intersect(env.render_aabb_to_local * ray.o, env.render_aabb_to_local * ray.d).x, 0.0f) + 1e-6f;
 	payload.origin = ray.o;
 	payload.dir = ray.d;
 	payload.t = t;
+	if (g_has_camera_ex && g_camera_ex.plane_z < 0.0f) { payload.alive = false; return; }   // slice plane, :1918-1928
 	if (!env.render_aabb.contains(env.render_aabb_to_local * ray.at(t))) { payload.alive = false; return; }
 	payload.alive = true;
 }
+
+// What the kernel leaves in frame_buffer[idx] / depth_buffer[idx] (:1912,1926,1946-1950): rgb cleared (alpha kept) or the envmap texel.
+void init_ray_background(uint32_t, uint32_t, const orc_view&, const MarchEnv&, const NerfPayload& payload, float* fb4, float* depth1) {
+	*depth1 = MAX_DEPTH;
+	const bool valid = !(payload.dir.x == 0.0f && payload.dir.y == 0.0f && payload.dir.z == 0.0f);
+	if (g_has_camera_ex && !valid) return;
+	if (g_has_camera_ex && g_camera_ex.plane_z < 0.0f) { *depth1 = -g_camera_ex.plane_z; return; }
+	if (g_env_w > 0) { vec4 e = read_envmap(payload.dir); fb4[0] = e.x; fb4[1] = e.y; fb4[2] = e.z; fb4[3] = e.w; }
+	else { fb4[0] = fb4[1] = fb4[2] = 0.0f; }
+}
+
+mat4x3 compositor_camera(const orc_view& view) { return g_has_camera_ex ? load_camera(g_camera_ex.camera1) : load_camera(view.camera); }
 
 // testbed_nerf.cu:334-363
 void advance_pos_nerf(NerfPayload& payload, const MarchEnv& env, uint32_t sample_index, float cone_angle_constant) {
@@ -404,6 +549,11 @@ float orc_march_to_occupied(const orc_model* model, const float* o, const float*
 	MarchEnv env = make_env(*model);
 	vec3 dir = {d[0], d[1], d[2]};
 	return if_unoccupied_advance_to_next_occupied_voxel(t, model->cone_angle_constant, {{o[0], o[1], o[2]}, dir}, 1.0f / dir, env);
+}
+void orc_set_camera_ex(const orc_camera_ex* ex) { g_has_camera_ex = ex != nullptr; if (ex) g_camera_ex = *ex; }
+void orc_set_envmap(const float* rgba, int32_t w, int32_t h) {
+	if (!rgba || w <= 0 || h <= 0) { g_envmap.clear(); g_env_w = g_env_h = 0; return; }
+	g_envmap.assign(rgba, rgba + (size_t)w * h * 4); g_env_w = w; g_env_h = h;
 }
 void orc_init_ray(const orc_view* view, const orc_model* model, uint32_t x, uint32_t y, float* out8) {
 	MarchEnv env = make_env(*model);

@@ -36,6 +36,12 @@ float ld_random_val(uint32_t index, uint32_t seed, uint32_t dim = 0);
 vec2 ld_random_pixel_offset(uint32_t spp);
 Ray uv_to_ray_pinhole(vec2 uv, ivec2 resolution, vec2 focal_length, const mat4x3& camera, vec2 screen_center);
 void init_ray_payload(uint32_t x, uint32_t y, const orc_view& view, const MarchEnv& env, NerfPayload& payload);
+// Stock-path extras (orc_set_camera_ex / orc_set_envmap). init_ray_background: what init_rays_with_payload_kernel_nerf leaves in the
+// frame / depth buffers for pixel (x, y) besides the payload; compositor_camera: the matrix Testbed::render_nerf hands to trace().
+extern bool g_has_camera_ex;
+extern orc_camera_ex g_camera_ex;
+void init_ray_background(uint32_t x, uint32_t y, const orc_view& view, const MarchEnv& env, const NerfPayload& payload, float* fb4, float* depth1);
+mat4x3 compositor_camera(const orc_view& view);
 void advance_pos_nerf(NerfPayload& payload, const MarchEnv& env, uint32_t sample_index, float cone_angle_constant);
 
 MarchEnv make_env(const orc_model& m);

@@ -36,6 +36,17 @@ typedef struct {
 	int32_t snap_to_pixel_centers;
 } orc_view;
 
+// The remaining arguments of init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1855-1880) for the stock path. Installed with
+// orc_set_camera_ex (a checker-wide override, like orc_set_grid_scales): NULL = pinhole, camera1 == camera0, no envmap.
+typedef struct {
+	float camera1[12];
+	float rolling_shutter[4];
+	float parallax_shift[3];
+	float near_distance, plane_z, aperture_size;
+	int32_t lens_mode;       // ELensMode (common.h:118-126): 0 Perspective, 1 OpenCV, 2 FTheta, 3 LatLong, 4 OpenCVFisheye, 5 Equirectangular
+	float lens_params[7];
+} orc_camera_ex;
+
 typedef struct {   // ObjectTransform (include/synerfgine/common.cuh:137-147) with host arrays
 	const float* nodes;   // n_nodes * 8 floats: bb.min[3], bb.max[3], left_idx(int), right_idx(int)
 	const float* tris;    // n_tris * 9 floats

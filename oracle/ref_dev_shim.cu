@@ -105,7 +105,14 @@ struct RefEngine {
 	GPUMemory<vec4> syn_acc_rgba, syn_fb; GPUMemory<float> syn_acc_depth, syn_fb_depth;
 	bool reset_color_buffer = true;
 	uint32_t last_n_hit = 0;
+	// stock-path camera extras (refdev_engine_set_camera_ex): the arguments Testbed::render_nerf forwards beyond the pinhole camera
+	bool has_ex = false;
+	mat4x3 camera1; vec4 rolling_shutter{0.0f, 0.0f, 0.0f, 1.0f}; vec3 parallax_shift{0.0f};
+	float near_distance = 0.0f, plane_z = 0.0f, aperture_size = 0.0f;
+	Lens lens{};
+	GPUMemory<vec4> envmap; ivec2 envmap_res{0};
 };
+struct RefCameraEx { float camera1[12]; float rolling_shutter[4]; float parallax_shift[3]; float near_distance, plane_z, aperture_size; int lens_mode; float lens_params[7]; };
 
 __global__ void k_dump_rand(uint32_t n, const curandState_t* __restrict__ st, uint32_t* __restrict__ out6, float* __restrict__ uniforms, uint32_t n_uniform) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -351,9 +358,13 @@ void ref_nerf_layer(RefEngine* e, RefModel* m, RefScene* s, const RefView& v, co
 	// Testbed::render clears the frame whenever accumulation restarts (view.render_buffer->clear_frame, testbed.cu:4375-4380); every call
 	// here is such a frame. init_rays_with_payload_kernel_nerf only rewrites rgb, so without this the alpha of a recycled allocation leaks in.
 	CUDA_CHECK_THROW(cudaMemsetAsync(e->nerf_fb.data(), 0, e->nerf_fb.size() * sizeof(vec4), stream));
-	tracer.init_rays_from_camera(v.spp, m->network->padded_output_width(), m->network->n_extra_dims(), res, focal, cam, cam, vec4(0.0f, 0.0f, 0.0f, 1.0f),
-	                             vec2(v.screen_center[0], v.screen_center[1]), vec3(0.0f), (bool)v.snap_to_pixel_centers, m->render_aabb, m->render_aabb_to_local, 0.0f /* near */,
-	                             0.0f /* plane_z: unused outside Slice mode */, 0.0f /* aperture */, Foveation{}, Lens{}, Buffer2DView<const vec4>{}, Buffer2DView<const vec2>{},
+	const bool ex = !alt && e->has_ex;
+	const mat4x3 cam1 = ex ? e->camera1 : cam;
+	const Buffer2DView<const vec4> envmap = (!alt && e->envmap_res.x > 0) ? Buffer2DView<const vec4>{e->envmap.data(), e->envmap_res} : Buffer2DView<const vec4>{};
+	tracer.init_rays_from_camera(v.spp, m->network->padded_output_width(), m->network->n_extra_dims(), res, focal, cam, cam1, ex ? e->rolling_shutter : vec4(0.0f, 0.0f, 0.0f, 1.0f),
+	                             vec2(v.screen_center[0], v.screen_center[1]), ex ? e->parallax_shift : vec3(0.0f), (bool)v.snap_to_pixel_centers, m->render_aabb, m->render_aabb_to_local,
+	                             ex ? e->near_distance : 0.0f, ex ? e->plane_z : 0.0f /* unused without aperture / Slice mode */, ex ? e->aperture_size : 0.0f, Foveation{}, ex ? e->lens : Lens{},
+	                             envmap, Buffer2DView<const vec2>{},
 	                             e->nerf_fb.data(), e->nerf_depth.data(), Buffer2DView<const uint8_t>{}, m->bitfield.data(), -1, m->max_cascade, m->cone_angle_constant, render_mode, stream);
 	const float depth_scale = 1.0f;
 	if (alt) {
@@ -378,7 +389,8 @@ void ref_nerf_layer(RefEngine* e, RefModel* m, RefScene* s, const RefView& v, co
 			CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
 		}
 	} else {
-		const uint32_t n_hit = tracer.trace(m->network, m->render_aabb, m->render_aabb_to_local, m->aabb, focal, m->cone_angle_constant, m->bitfield.data(), render_mode, cam, depth_scale,
+		// Testbed::render_nerf passes camera_matrix1 to trace() and camera_matrix0 to shade_kernel_nerf (testbed_nerf.cu:2761,2815)
+		const uint32_t n_hit = tracer.trace(m->network, m->render_aabb, m->render_aabb_to_local, m->aabb, focal, m->cone_angle_constant, m->bitfield.data(), render_mode, cam1, depth_scale,
 		                                    0, -1, m->rgb_activation, m->density_activation, -1, m->max_cascade, m->min_transmittance, 0.0f, 0, nullptr, stream);
 		e->last_n_hit = n_hit;
 		RaysNerfSoa& rays_hit = tracer.rays_hit();
@@ -465,19 +477,47 @@ EXPORT int refdev_engine_read(void* engine, int which, float* out_host) {
 }
 EXPORT uint32_t refdev_engine_last_n_hit(void* engine) { return ((RefEngine*)engine)->last_n_hit; }
 
+// Camera extras + environment map of the following stock-path renders (refdev_render_nerf with alt = 0). ex = NULL: pinhole; envmap = NULL: none.
+EXPORT int refdev_engine_set_camera_ex(void* engine, const RefCameraEx* ex, const float* envmap_rgba_host, int env_w, int env_h) {
+	RefEngine* e = (RefEngine*)engine;
+	return guarded([&] {
+		e->has_ex = ex != nullptr;
+		if (ex) {
+			e->camera1 = M43(ex->camera1);
+			e->rolling_shutter = vec4(ex->rolling_shutter[0], ex->rolling_shutter[1], ex->rolling_shutter[2], ex->rolling_shutter[3]);
+			e->parallax_shift = V3(ex->parallax_shift);
+			e->near_distance = ex->near_distance; e->plane_z = ex->plane_z; e->aperture_size = ex->aperture_size;
+			e->lens = Lens{}; e->lens.mode = (ELensMode)ex->lens_mode;
+			for (int i = 0; i < 7; ++i) e->lens.params[i] = ex->lens_params[i];
+		}
+		if (envmap_rgba_host && env_w > 0 && env_h > 0) {
+			e->envmap.resize((size_t)env_w * env_h);
+			CUDA_CHECK_THROW(cudaMemcpy(e->envmap.data(), envmap_rgba_host, (size_t)env_w * env_h * sizeof(vec4), cudaMemcpyHostToDevice));
+			e->envmap_res = ivec2(env_w, env_h);
+		} else e->envmap_res = ivec2(0);
+	});
+}
+
 // ---- small taps -----------------------------------------------------------------------------------------------------------------------
 // Ray set-up + start jitter exactly as NerfTracer::init_rays_from_camera leaves the payloads (testbed_nerf.cu:2037-2120): out n x 8 floats
 // {origin3, dir3, t, alive}.
-EXPORT int refdev_init_rays(void* model, const RefView* v, int w, int h, float* out_host) {
-	RefModel* m = (RefModel*)model;
+static int init_rays_impl(RefModel* m, const RefView* v, int w, int h, const RefCameraEx* ex, float* out_host);
+EXPORT int refdev_init_rays(void* model, const RefView* v, int w, int h, float* out_host) { return init_rays_impl((RefModel*)model, v, w, h, nullptr, out_host); }
+// The same with the camera extras of uv_to_ray (lens, aperture, parallax, near plane, end-of-shutter camera).
+EXPORT int refdev_init_rays_ex(void* model, const RefView* v, int w, int h, const RefCameraEx* ex, float* out_host) { return init_rays_impl((RefModel*)model, v, w, h, ex, out_host); }
+static int init_rays_impl(RefModel* m, const RefView* v, int w, int h, const RefCameraEx* ex, float* out_host) {
 	return guarded([&] {
 		const size_t n = (size_t)w * h;
 		GPUMemory<vec4> fb(n); GPUMemory<float> depth(n);
 		Testbed::NerfTracer tracer;
 		const mat4x3 cam = M43(v->camera);
-		tracer.init_rays_from_camera(v->spp, m->network->padded_output_width(), 0, ivec2(w, h), vec2(v->focal_length[0], v->focal_length[1]), cam, cam, vec4(0.0f, 0.0f, 0.0f, 1.0f),
-		                             vec2(v->screen_center[0], v->screen_center[1]), vec3(0.0f), (bool)v->snap_to_pixel_centers, m->render_aabb, m->render_aabb_to_local, 0.0f, 0.0f, 0.0f,
-		                             Foveation{}, Lens{}, Buffer2DView<const vec4>{}, Buffer2DView<const vec2>{}, fb.data(), depth.data(), Buffer2DView<const uint8_t>{}, m->bitfield.data(), -1,
+		Lens lens{};
+		if (ex) { lens.mode = (ELensMode)ex->lens_mode; for (int i = 0; i < 7; ++i) lens.params[i] = ex->lens_params[i]; }
+		tracer.init_rays_from_camera(v->spp, m->network->padded_output_width(), 0, ivec2(w, h), vec2(v->focal_length[0], v->focal_length[1]), cam, ex ? M43(ex->camera1) : cam,
+		                             ex ? vec4(ex->rolling_shutter[0], ex->rolling_shutter[1], ex->rolling_shutter[2], ex->rolling_shutter[3]) : vec4(0.0f, 0.0f, 0.0f, 1.0f),
+		                             vec2(v->screen_center[0], v->screen_center[1]), ex ? V3(ex->parallax_shift) : vec3(0.0f), (bool)v->snap_to_pixel_centers, m->render_aabb, m->render_aabb_to_local,
+		                             ex ? ex->near_distance : 0.0f, ex ? ex->plane_z : 0.0f, ex ? ex->aperture_size : 0.0f,
+		                             Foveation{}, lens, Buffer2DView<const vec4>{}, Buffer2DView<const vec2>{}, fb.data(), depth.data(), Buffer2DView<const uint8_t>{}, m->bitfield.data(), -1,
 		                             m->max_cascade, m->cone_angle_constant, ERenderMode::Shade, nullptr);
 		std::vector<NerfPayload> pl(n);
 		CUDA_CHECK_THROW(cudaMemcpy(pl.data(), tracer.rays_init().payload, n * sizeof(NerfPayload), cudaMemcpyDeviceToHost));

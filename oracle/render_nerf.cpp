@@ -182,7 +182,7 @@ static uint64_t render_nerf_per_ray(const orc_model* model, const orc_view* view
 	MarchEnv env = make_env(*model);
 	NetworkView net = make_network_view(*model);
 	BoundingBox train_aabb = load_aabb(model->aabb_min, model->aabb_max);
-	mat4x3 cam = load_camera(view->camera);
+	mat4x3 cam = alt ? load_camera(view->camera) : compositor_camera(*view);   // trace() gets camera_matrix1 (testbed_nerf.cu:2761)
 	const uint32_t N = (uint32_t)view->width * view->height;
 	if (positions) std::memset(positions, 0, sizeof(float) * 3 * N);
 	uint64_t n_samples = 0;
@@ -191,8 +191,7 @@ static uint64_t render_nerf_per_ray(const orc_model* model, const orc_view* view
 		RayState r;
 		init_ray_payload(x, y, *view, env, r.p);
 		uint32_t idx = r.p.idx;
-		depth[idx] = MAX_DEPTH;
-		fb[idx * 4 + 0] = fb[idx * 4 + 1] = fb[idx * 4 + 2] = 0.0f; // envmap-less clear, testbed_nerf.cu:1952
+		init_ray_background(x, y, *view, env, r.p, fb + (size_t)idx * 4, depth + idx); // rgb clear or envmap texel, testbed_nerf.cu:1946-1952
 		r.rgba = {0, 0, 0, 0}; r.depth = 0.0f;
 		advance_pos_nerf(r.p, env, view->spp, model->cone_angle_constant);
 		bool finished = !r.p.alive; // rays dead before the first iteration are compacted in iteration 1
@@ -220,15 +219,14 @@ uint64_t orc_render_nerf_wavefront(const orc_model* model, const orc_view* view,
 	MarchEnv env = make_env(*model);
 	NetworkView net = make_network_view(*model);
 	BoundingBox train_aabb = load_aabb(model->aabb_min, model->aabb_max);
-	mat4x3 cam = load_camera(view->camera);
+	mat4x3 cam = alt ? load_camera(view->camera) : compositor_camera(*view);   // trace() gets camera_matrix1 (testbed_nerf.cu:2761)
 	const uint32_t N = (uint32_t)view->width * view->height;
 	if (positions) std::memset(positions, 0, sizeof(float) * 3 * N);
 	std::vector<RayState> rays(N);
 	for (int y = 0; y < view->height; ++y) for (int x = 0; x < view->width; ++x) {
 		RayState& r = rays[x + view->width * y];
 		init_ray_payload(x, y, *view, env, r.p);
-		depth[r.p.idx] = MAX_DEPTH;
-		fb[r.p.idx * 4 + 0] = fb[r.p.idx * 4 + 1] = fb[r.p.idx * 4 + 2] = 0.0f;
+		init_ray_background(x, y, *view, env, r.p, fb + (size_t)r.p.idx * 4, depth + r.p.idx);
 		r.rgba = {0, 0, 0, 0}; r.depth = 0.0f;
 		advance_pos_nerf(r.p, env, view->spp, model->cone_angle_constant);
 	}

@@ -26,6 +26,15 @@ class View(C.Structure):
                 ("spp", u32), ("snap_to_pixel_centers", i32)]
 
 
+class CameraEx(C.Structure):
+    """snb_camera_ex: the stock render's camera beyond the pinhole (end-of-shutter camera, rolling shutter, parallax, near plane, DoF, lens)."""
+    _fields_ = [("camera1", f32 * 12), ("rolling_shutter", f32 * 4), ("parallax_shift", f32 * 3), ("near_distance", f32), ("plane_z", f32),
+                ("aperture_size", f32), ("lens_mode", i32), ("lens_params", f32 * 7)]
+
+
+LENS_MODES = {"perspective": 0, "opencv": 1, "ftheta": 2, "latlong": 3, "opencv_fisheye": 4, "equirectangular": 5}
+
+
 class Tile(C.Structure):
     _fields_ = [("x0", i32), ("y0", i32), ("w", i32), ("h", i32)]
 
@@ -91,6 +100,9 @@ SIGNATURES = {
     "snb_rng_tap": (C.c_int, [vp, u64, u32, u32, vp, vp]),
     "snb_get_alt_status": (C.c_int, [vp, C.POINTER(u32)]),
     "snb_set_alt_schedule": (C.c_int, [vp, C.POINTER(u8), u32]),
+    "snb_set_camera_ex": (C.c_int, [vp, C.POINTER(CameraEx)]),
+    "snb_set_envmap": (C.c_int, [vp, pf32, i32, i32]),
+    "snb_camera_log_lerp": (C.c_int, [pf32, pf32, f32, pf32]),
     "snb_launch_count": (u64, [vp]),
     "snb_scene_load_json": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),
     "snb_scene_free": (None, [vp]),

@@ -77,6 +77,10 @@ struct snb_ctx {
 	int alt_batch = 8;                 // batch length of alt_mode 2
 	uint32_t alt_target_queries = 2u * 1024u * 1024u;   // target_n_queries of trace_alt (src/testbed_nerf.cu:2188)
 	snb::DevBuf d_alt;
+	// stock-path camera extras (snb_set_camera_ex / snb_set_envmap); cam_ex.enabled == 0 and no envmap: plain pinhole ray generation
+	snb::CameraEx cam_ex = {};
+	bool has_cam_ex = false;
+	snb::DevBuf d_envmap; int env_w = 0, env_h = 0;
 
 	// per-stage device timing of the last frame (CUDA events on the context's stream; see snb_get_stage_ms)
 	static const int kStages = 5;   // 0 nerf raygen, 1 nerf fused march, 2 nerf normals+shadows, 3 mesh layer, 4 overlay

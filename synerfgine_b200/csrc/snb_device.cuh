@@ -37,6 +37,21 @@ struct DevModel {
 	MarchEnv env;
 };
 
+// The rest of Testbed::render_nerf's camera model (uv_to_ray, include/neural-graphics-primitives/common_device.cuh:403-470, and the
+// arguments of init_rays_with_payload_kernel_nerf, src/testbed_nerf.cu:1855-1970): end-of-shutter camera + rolling shutter (motion blur),
+// parallax shift, near plane, thin-lens aperture focused at plane_z, lens models, environment map. enabled == 0: the plain pinhole path.
+enum { kLensPerspective = 0, kLensOpenCV = 1, kLensFTheta = 2, kLensLatLong = 3, kLensOpenCVFisheye = 4, kLensEquirectangular = 5 };
+struct CameraEx {
+	int enabled;
+	m4x3 cam1;
+	float rolling[4];
+	v3 parallax;
+	float near_distance, plane_z, aperture;
+	int lens_mode;
+	float lens[7];
+	const float4* envmap; int env_w, env_h;
+};
+
 struct DevView {
 	m4x3 cam;
 	v2 focal, center;
@@ -45,6 +60,7 @@ struct DevView {
 	uint32_t spp;
 	int snap;
 	v2 pix_off;                  // ld_pixel_offset(snap ? 0 : spp), evaluated once on the host
+	CameraEx ex;
 };
 
 struct DevObject {               // sng::ObjectTransform with precomputed world->object map

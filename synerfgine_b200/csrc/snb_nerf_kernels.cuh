@@ -204,6 +204,7 @@ __global__ void __launch_bounds__(128) k_bitfield_to_linear(const uint8_t* __res
 
 // ---- ray generation: one thread per tile pixel, 8x4 pixel patches per warp so queue neighbours are image neighbours ----
 // Patches [patch_begin, patch_end) of the tile (row-major patch order): one launch per band of the frame.
+template <bool EX>
 __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env, NerfOut out, RayRec* __restrict__ queue, unsigned int* __restrict__ queue_tail,
                                                      int patch_begin, int patch_end) {
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -220,8 +221,15 @@ __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env,
 		out.depth[lidx] = kMaxDepth;
 		if (out.positions) { out.positions[lidx * 3 + 0] = 0.0f; out.positions[lidx * 3 + 1] = 0.0f; out.positions[lidx * 3 + 2] = 0.0f; }
 		v3 o, d; float t;
-		alive = nerf_primary_ray(x, y, view, env, o, d, t);
+		bool valid = true;
+		alive = nerf_primary_ray<EX>(x, y, view, env, o, d, t, &valid);
 		const uint32_t idx = (uint32_t)x + (uint32_t)view.width * (uint32_t)y;
+		if (EX && view.ex.enabled) {
+			// init_rays_with_payload_kernel_nerf, src/testbed_nerf.cu:1918-1950: a negative plane_z (slice plane) kills the ray and writes the
+			// plane depth; the environment map is the background of every valid ray, whether it meets the render box or not.
+			if (valid && view.ex.plane_z < 0.0f) { alive = false; out.depth[lidx] = -view.ex.plane_z; }
+			else if (valid && view.ex.envmap) out.fb[lidx] = envmap_lookup(view.ex, d);
+		}
 		if (alive) {
 			// start jitter + skip to the first occupied cell (advance_pos_nerf)
 			const v3 idir = 1.0f / d;
@@ -261,7 +269,11 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 	} else if (render_mode == 1) {
 		tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z);
 	}
-	out.fb[l] = tmp;   // frame buffer was cleared to 0 by ray generation: tmp + 0 * (1 - a)
+	if (!alt && view.ex.enabled && view.ex.envmap) {
+		// shade_kernel_nerf, src/testbed_nerf.cu:1824: frame_buffer = tmp + frame_buffer * (1 - tmp.a) over the environment map
+		const float4 bg = out.fb[l]; const float k = 1.0f - tmp.w;
+		out.fb[l] = make_float4(tmp.x + bg.x * k, tmp.y + bg.y * k, tmp.z + bg.z * k, tmp.w + bg.w * k);
+	} else out.fb[l] = tmp;   // frame buffer was cleared to 0 by ray generation: tmp + 0 * (1 - a)
 	if (tmp.w > 0.2f) out.depth[l] = depth;
 }
 
@@ -496,7 +508,7 @@ __global__ void __launch_bounds__(128) k_march_trace(DevView view, MarchEnv env,
 	if (ray >= (uint32_t)(view.width * view.height)) return;
 	const int x = (int)(ray % (uint32_t)view.width), y = (int)(ray / (uint32_t)view.width);
 	v3 o, d; float t;
-	bool alive = nerf_primary_ray(x, y, view, env, o, d, t);
+	bool alive = nerf_primary_ray<true>(x, y, view, env, o, d, t);
 	if (alive) {
 		const v3 idir0 = 1.0f / d;
 		t = advance_steps(t, env.st, ld_value(view.spp, ray * 786433u));

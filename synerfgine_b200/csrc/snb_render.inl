@@ -10,6 +10,19 @@ static DevView make_view(const snb_view* v, const snb_tile* tile) {
 	else { d.tx0 = 0; d.ty0 = 0; d.tw = v->width; d.th = v->height; }
 	d.spp = v->spp; d.snap = v->snap_to_pixel_centers;
 	d.pix_off = ld_pixel_offset(d.snap ? 0u : d.spp);
+	d.ex = CameraEx{};
+	return d;
+}
+
+// The stock path's view: the context's camera extras and environment map on top of the pinhole view.
+static DevView make_stock_view(snb_ctx* c, const snb_view* v, const snb_tile* tile) {
+	DevView d = make_view(v, tile);
+	const bool env = c->env_w > 0 && c->env_h > 0;
+	if (!c->has_cam_ex && !env) return d;
+	if (c->has_cam_ex) d.ex = c->cam_ex;
+	else { d.ex.cam1 = d.cam; d.ex.rolling[3] = 1.0f; d.ex.plane_z = 1.0f; }   // envmap alone: camera1 = camera0, nothing else
+	d.ex.enabled = 1;
+	d.ex.envmap = env ? c->d_envmap.as<float4>() : nullptr; d.ex.env_w = c->env_w; d.ex.env_h = c->env_h;
 	return d;
 }
 
@@ -91,13 +104,19 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	const int patches = patches_x * patches_y;
 	RayRec* q0 = c->d_queue.as<RayRec>();
 	c->stage_begin(0);
-	k_nerf_raygen<<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, patches);
+	if (dv.ex.enabled) k_nerf_raygen<true><<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, patches);
+	else k_nerf_raygen<false><<<(patches + 3) / 4, 128, 0, c->stream>>>(dv, c->model.env, out, q0, qctl, 0, patches);
 	SNB_LAUNCHED(c);
 	c->stage_end(0);
 	c->stage_begin(1);
 	int rc = SNB_OK;
 	AltCtl ctl; ctl.st = nullptr; ctl.target_queries = c->alt_target_queries; ctl.fixed_steps = 0; ctl.conditional = 0; ctl.external = c->alt_mode == 1;
-	if (!alt) rc = launch_fused_f<false>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl);
+	if (!alt) {
+		// Testbed::render_nerf hands camera_matrix1 to the compositor (src/testbed_nerf.cu:2761): depth is measured along the END-of-shutter camera
+		DevView mv = dv;
+		if (dv.ex.enabled) mv.cam = dv.ex.cam1;
+		rc = launch_fused_f<false>(c, mv, out, render_mode, patches * 32, q0, qctl, ctl);
+	}
 	else if (c->alt_mode == 2) { ctl.fixed_steps = (uint32_t)c->alt_batch; rc = launch_fused_f<true>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl); }
 	else {
 		AltState* st = c->d_alt.as<AltState>();
@@ -214,7 +233,7 @@ int snb_render_nerf(snb_ctx* c, const snb_view* view, const snb_tile* tile, int 
 	if (!c || !fb || !depth) return SNB_ERR_ARG;
 	int rc = check_view(c, view, tile); if (rc) return rc;
 	SNB_CUDA(c, cudaSetDevice(c->device));
-	return render_nerf_layer(c, make_view(view, tile), false, render_mode, fb, depth, nullptr);
+	return render_nerf_layer(c, make_stock_view(c, view, tile), false, render_mode, fb, depth, nullptr);
 }
 
 int snb_render_syn(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* syn_rgba, float* syn_depth) {

@@ -439,4 +439,96 @@ int snb_camera_from_view(const float* view3, const float* at3, float zoom, float
 	return SNB_OK;
 }
 
+// ---- camera_log_lerp (include/neural-graphics-primitives/common_device.cuh:658-660): exp(log(B * A^-1) * t) * A on 4x4 matrices, fp32,
+// with tcnn's matrix functions (vec.h:880-958): Denman-Beavers square roots until the matrix is within 1e-5 of the identity, the
+// Mercator series for the logarithm, scaling-and-squaring with a (6,6) Pade approximant for the exponential.
 } // extern "C"
+
+namespace {
+struct M4 { float m[4][4]; };   // m[column][row]
+M4 m4_identity() { M4 r{}; for (int i = 0; i < 4; ++i) r.m[i][i] = 1.0f; return r; }
+M4 m4_mul(const M4& a, const M4& b) {
+	M4 r{};
+	for (int c = 0; c < 4; ++c) for (int row = 0; row < 4; ++row) { float acc = 0.0f; for (int k = 0; k < 4; ++k) acc += a.m[k][row] * b.m[c][k]; r.m[c][row] = acc; }
+	return r;
+}
+M4 m4_add(const M4& a, const M4& b) { M4 r; for (int c = 0; c < 4; ++c) for (int k = 0; k < 4; ++k) r.m[c][k] = a.m[c][k] + b.m[c][k]; return r; }
+M4 m4_sub(const M4& a, const M4& b) { M4 r; for (int c = 0; c < 4; ++c) for (int k = 0; k < 4; ++k) r.m[c][k] = a.m[c][k] - b.m[c][k]; return r; }
+M4 m4_scale(float s, const M4& a) { M4 r; for (int c = 0; c < 4; ++c) for (int k = 0; k < 4; ++k) r.m[c][k] = s * a.m[c][k]; return r; }
+float m4_frobenius(const M4& a) { float acc = 0.0f; for (int c = 0; c < 4; ++c) for (int k = 0; k < 4; ++k) acc += a.m[c][k] * a.m[c][k]; return std::sqrt(acc); }
+M4 m4_inverse(const M4& a) {   // Gauss-Jordan with partial pivoting
+	float w[4][8];
+	for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { w[r][c] = a.m[c][r]; w[r][4 + c] = r == c ? 1.0f : 0.0f; }
+	for (int col = 0; col < 4; ++col) {
+		int piv = col;
+		for (int r = col + 1; r < 4; ++r) if (std::fabs(w[r][col]) > std::fabs(w[piv][col])) piv = r;
+		if (piv != col) for (int c = 0; c < 8; ++c) std::swap(w[piv][c], w[col][c]);
+		const float d = w[col][col];
+		for (int c = 0; c < 8; ++c) w[col][c] /= d;
+		for (int r = 0; r < 4; ++r) if (r != col) { const float f = w[r][col]; if (f != 0.0f) for (int c = 0; c < 8; ++c) w[r][c] -= f * w[col][c]; }
+	}
+	M4 out;
+	for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out.m[c][r] = w[r][4 + c];
+	return out;
+}
+M4 m4_sqrt(const M4& m) {
+	M4 X = m, Y = m4_identity();
+	for (int i = 0; i < 32; ++i) {
+		if (m4_frobenius(m4_sub(m4_mul(X, X), m)) < 1e-10f) return X;
+		const M4 iX = m4_inverse(X);
+		X = m4_scale(0.5f, m4_add(X, m4_inverse(Y)));
+		Y = m4_scale(0.5f, m4_add(Y, iX));
+	}
+	return X;
+}
+M4 m4_log(const M4& m) {
+	M4 r = m;
+	int j = 0;
+	for (; j < 32; ++j) {
+		if (m4_frobenius(m4_sub(r, m4_identity())) < 1e-5f) break;
+		r = m4_sqrt(r);
+	}
+	const M4 A = m4_sub(r, m4_identity());
+	M4 Z = A, X = A;
+	for (int i = 2; i < 32; ++i) {
+		if (m4_frobenius(Z) < 1e-10f) break;
+		Z = m4_mul(Z, A);
+		X = m4_add(X, m4_scale(1.0f / (float)i, Z));
+	}
+	return m4_scale(std::ldexp(1.0f, j), X);
+}
+M4 m4_exp(const M4& m) {
+	const float norm = m4_frobenius(m);
+	const int squarings = norm > 0.0f ? std::max(0, 1 + (int)std::floor(std::log2(norm))) : 0;
+	const M4 a = m4_scale(std::ldexp(1.0f, -squarings), m);
+	M4 mX = m4_identity(), mD = m4_identity(), mN = m4_identity();
+	float c = 1.0f, sgn = -1.0f;
+	const int q = 6;
+	for (int k = 1; k <= q; ++k) {
+		c = c * (float)(q - k + 1) / (float)(k * (2 * q - k + 1));
+		mX = m4_mul(a, mX);
+		const M4 cmX = m4_scale(c, mX);
+		mN = m4_add(mN, cmX);
+		mD = m4_add(mD, m4_scale(sgn, cmX));
+		sgn = -sgn;
+	}
+	M4 r = m4_mul(m4_inverse(mD), mN);
+	for (int i = 0; i < squarings; ++i) r = m4_mul(r, r);
+	return r;
+}
+M4 m4_from_camera(const float* c12) { M4 r = m4_identity(); for (int c = 0; c < 4; ++c) for (int k = 0; k < 3; ++k) r.m[c][k] = c12[c * 3 + k]; return r; }
+}  // namespace
+
+extern "C" {
+
+// ≙ camera_log_lerp: the end-of-shutter camera of one motion-blur sample (src/python_api.cu:161: camera_log_lerp(start, end, shutter_fraction)).
+int snb_camera_log_lerp(const float* a12, const float* b12, float t, float* out12) {
+	if (!a12 || !b12 || !out12) return SNB_ERR_ARG;
+	const M4 A = m4_from_camera(a12), B = m4_from_camera(b12);
+	const M4 r = m4_mul(m4_exp(m4_scale(t, m4_log(m4_mul(B, m4_inverse(A))))), A);
+	for (int c = 0; c < 4; ++c) for (int k = 0; k < 3; ++k) out12[c * 3 + k] = r.m[c][k];
+	return SNB_OK;
+}
+
+} // extern "C"
+

@@ -67,7 +67,7 @@ int snb_march_trace(snb_ctx* c, const snb_view* view, uint32_t max_samples, floa
 	int rc = check_view(c, view, nullptr); if (rc) return rc;
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model");
 	SNB_CUDA(c, cudaSetDevice(c->device));
-	const DevView dv = make_view(view, nullptr);
+	const DevView dv = make_stock_view(c, view, nullptr);
 	const uint32_t n = (uint32_t)(dv.width * dv.height);
 	k_march_trace<<<(n + 127) / 128, 128, 0, c->stream>>>(dv, c->model.env, max_samples, t_dev, dt_dev, cell_dev, n_dev, origin_dir_dev);
 	SNB_LAUNCHED(c);
@@ -156,6 +156,34 @@ int snb_set_alt_schedule(snb_ctx* c, const uint8_t* steps, uint32_t n) {
 	for (int j = 0; j < kAltSched; ++j) sched[j] = (uint32_t)j < n ? steps[j] : (n ? (uint8_t)8 : (uint8_t)0);
 	SNB_CUDA(c, cudaMemcpyAsync(c->d_alt.as<unsigned char>() + offsetof(AltState, sched), sched, sizeof sched, cudaMemcpyHostToDevice, c->stream));
 	SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // `sched` is a stack array
+	return SNB_OK;
+}
+
+int snb_set_camera_ex(snb_ctx* c, const snb_camera_ex* ex) {
+	if (!c) return SNB_ERR_ARG;
+	if (!ex) { c->has_cam_ex = false; c->cam_ex = CameraEx{}; return SNB_OK; }
+	if (ex->lens_mode < 0 || ex->lens_mode > SNB_LENS_EQUIRECTANGULAR) return c->fail(SNB_ERR_ARG, "unknown lens mode");
+	if (ex->aperture_size != 0.0f && ex->plane_z == 0.0f) return c->fail(SNB_ERR_ARG, "an open aperture needs a focus distance (plane_z != 0)");
+	CameraEx e = {};
+	e.enabled = 1;
+	e.cam1.c0 = ld3(ex->camera1); e.cam1.c1 = ld3(ex->camera1 + 3); e.cam1.c2 = ld3(ex->camera1 + 6); e.cam1.c3 = ld3(ex->camera1 + 9);
+	for (int i = 0; i < 4; ++i) e.rolling[i] = ex->rolling_shutter[i];
+	e.parallax = ld3(ex->parallax_shift);
+	e.near_distance = ex->near_distance; e.plane_z = ex->plane_z; e.aperture = ex->aperture_size;
+	e.lens_mode = ex->lens_mode;
+	for (int i = 0; i < 7; ++i) e.lens[i] = ex->lens_params[i];
+	c->cam_ex = e; c->has_cam_ex = true;
+	return SNB_OK;
+}
+
+int snb_set_envmap(snb_ctx* c, const float* rgba_host, int32_t w, int32_t h) {
+	if (!c) return SNB_ERR_ARG;
+	if (!rgba_host || w <= 0 || h <= 0) { c->env_w = c->env_h = 0; return SNB_OK; }
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, c->d_envmap.reserve((size_t)w * h * 16));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_envmap.p, rgba_host, (size_t)w * h * 16, cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, cudaStreamSynchronize(c->stream));   // the caller's buffer may go away
+	c->env_w = w; c->env_h = h;
 	return SNB_OK;
 }
 

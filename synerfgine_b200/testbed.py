@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import RtParams, Tile, View  # noqa: F401
+from ._lib import LENS_MODES, CameraEx, RtParams, Tile, View  # noqa: F401
 from .scene import Scene  # noqa: F401
 
 
@@ -46,6 +46,22 @@ class Testbed:
         self.render_mode = 1        # ERenderMode::Shade
         self.tonemap_curve = 0
         self.snap_to_pixel_centers = True
+        # the rest of the stock render's camera (testbed.h: m_aperture_size, m_slice_plane_z, m_parallax_shift, m_render_near_distance,
+        # m_nerf.render_with_lens_distortion / render_lens, m_envmap); all off by default = the pinhole path
+        self.aperture_size = 0.0
+        self.slice_plane_z = 0.0
+        self.parallax_shift = (0.0, 0.0, 0.0)
+        self.render_near_distance = 0.0
+        self.render_with_lens_distortion = False
+        self.render_lens_mode = "perspective"
+        self.render_lens_params = (0.0,) * 7
+        self.envmap = None            # float32 [h, w, 4] or None
+        self._envmap_uploaded = None
+        # camera path of render(start_t, end_t): callable t in [0, 1] -> camera matrix [4, 3] (columns). The reference evaluates its
+        # CameraPath spline here (set_camera_from_time, src/testbed.cu:2203-2216); the spline editor itself is GUI state (out of scope),
+        # so the path is whatever the caller supplies, e.g. camera_path_from_keyframes(). None = the camera stays (as with an empty path).
+        self.camera_path = None
+        self.smoothed_camera = None
         self.model = None
         self._accum = None
         self._spp = 0
@@ -146,19 +162,94 @@ class Testbed:
         self._check(self.lib.snb_sync(self.ctx), "snb_sync")
         return fb, depth
 
+    def _camera_extras(self, camera0, camera1):
+        """snb_camera_ex of one sample, or None when every extra is off and the shutter does not move (-> pinhole path)."""
+        lens = self.render_with_lens_distortion and self.render_lens_mode != "perspective"
+        moving = not np.array_equal(np.asarray(camera0, np.float32), np.asarray(camera1, np.float32))
+        if not (lens or moving or self.aperture_size != 0.0 or self.render_near_distance != 0.0 or any(self.parallax_shift)):
+            return None
+        ex = CameraEx()
+        ex.camera1[:] = [float(x) for x in np.asarray(camera1, np.float32).reshape(-1)]
+        ex.rolling_shutter[:] = [0.0, 0.0, 0.0, 1.0]            # python_api.cu:181
+        ex.parallax_shift[:] = [float(x) for x in self.parallax_shift]
+        ex.near_distance = float(self.render_near_distance)
+        ex.plane_z = float(self.slice_plane_z) + float(self.scale)  # testbed_nerf.cu:2693 (the Slice view's negated plane is a GUI debug mode)
+        ex.aperture_size = float(self.aperture_size)
+        ex.lens_mode = LENS_MODES[self.render_lens_mode] if lens else 0
+        ex.lens_params[:] = [float(x) for x in self.render_lens_params] if lens else [0.0] * 7
+        return ex
+
+    def _sync_envmap(self):
+        if self.envmap is self._envmap_uploaded:
+            return
+        if self.envmap is None:
+            self._check(self.lib.snb_set_envmap(self.ctx, None, 0, 0), "snb_set_envmap")
+        else:
+            e = np.ascontiguousarray(self.envmap, dtype=np.float32)
+            if e.ndim != 3 or e.shape[2] != 4:
+                raise ValueError("envmap must be float32 [h, w, 4]")
+            self._check(self.lib.snb_set_envmap(self.ctx, _fp(e), e.shape[1], e.shape[0]), "snb_set_envmap")
+        self._envmap_uploaded = self.envmap
+
+    def camera_log_lerp(self, a, b, t):
+        """≙ camera_log_lerp (common_device.cuh:658-660) evaluated by the host library."""
+        a = np.ascontiguousarray(a, np.float32).reshape(-1); b = np.ascontiguousarray(b, np.float32).reshape(-1)
+        out = np.zeros(12, np.float32)
+        if self.lib.snb_camera_log_lerp(_fp(a), _fp(b), float(t), _fp(out)) != 0:
+            raise _lib.SnbError("snb_camera_log_lerp failed")
+        return out.reshape(4, 3)
+
+    def set_camera_from_time(self, t):
+        """≙ Testbed::set_camera_from_time: no path, no change."""
+        if self.camera_path is not None:
+            self.camera_matrix = np.asarray(self.camera_path(float(t)), dtype=np.float32).reshape(4, 3).copy()
+
+    def render_sample(self, width, height, spp_index, camera0, camera1, tile=None):
+        """One sample of the stock render (render_frame -> render_nerf) with the shutter open from camera0 to camera1."""
+        self._sync_envmap()
+        ex = self._camera_extras(camera0, camera1)
+        self._check(self.lib.snb_set_camera_ex(self.ctx, C.byref(ex) if ex is not None else None), "snb_set_camera_ex")
+        saved = self.camera_matrix
+        self.camera_matrix = np.asarray(camera0, dtype=np.float32).reshape(4, 3)
+        try:
+            return self.render_nerf_raw(width, height, spp_index=spp_index, tile=tile)
+        finally:
+            self.camera_matrix = saved
+
     def render(self, width=1920, height=1080, spp=1, linear=True, start_t=-1.0, end_t=-1.0, fps=30.0, shutter_fraction=1.0):
-        """≙ pyngp.Testbed.render: accumulate ``spp`` samples, tonemap, return float32 ndarray [H, W, 4]."""
-        if start_t >= 0 or end_t >= 0:
-            raise NotImplementedError("camera-path motion blur (start_t/end_t) is SURVEY §8(f) rank 4")
+        """≙ pyngp.Testbed.render (src/python_api.cu:105-205): accumulate ``spp`` samples, tonemap, return float32 ndarray [H, W, 4].
+        With start_t >= 0 the camera follows ``camera_path`` from start_t to end_t while the shutter is open for ``shutter_fraction`` of
+        the frame: every sample's rays interpolate per pixel between the start camera and camera_log_lerp(start, end, shutter_fraction)."""
+        if end_t < 0.0:
+            end_t = start_t
+        path_animation = start_t >= 0.0
+        if not path_animation or self.smoothed_camera is None:
+            self.smoothed_camera = np.asarray(self.camera_matrix, np.float32).copy()
+        if start_t == 0.0:
+            self.set_camera_from_time(start_t)
+            self.smoothed_camera = self.camera_matrix.copy()
+        start_cam = self.smoothed_camera.copy()
+        if path_animation:
+            self.set_camera_from_time(end_t)
+            self.smoothed_camera = self.camera_matrix.copy()     # apply_camera_smoothing with m_camera_smoothing off (the default)
+        end_cam = self.smoothed_camera.copy()
         n = width * height
         accum = torch.zeros((n, 4), dtype=torch.float32, device=self.device)
         out = torch.empty((n, 4), dtype=torch.float32, device=self.device)
+        torch.cuda.current_stream(self.device).synchronize()   # the zero fill runs on torch's stream, the context on its own
         bg = np.asarray(self.background_color, dtype=np.float32)
+        moving = not np.array_equal(start_cam, end_cam)
+        sample_end = self.camera_log_lerp(start_cam, end_cam, shutter_fraction) if moving else start_cam
         for i in range(spp):
-            fb, _ = self.render_nerf_raw(width, height, spp_index=i)
+            if path_animation:
+                a0, a1 = i / spp * shutter_fraction, (i + 1.0) / spp * shutter_fraction
+                self.set_camera_from_time(start_t + (end_t - start_t) * (a0 + a1) / 2.0)
+            fb, _ = self.render_sample(width, height, i, start_cam, sample_end)
             self._check(self.lib.snb_accumulate_tonemap(self.ctx, n, fb.data_ptr(), accum.data_ptr(), i, 0, 0 if linear else 1, float(self.exposure),
                                                         _fp(bg), self.tonemap_curve, out.data_ptr()), "snb_accumulate_tonemap")
         self._check(self.lib.snb_sync(self.ctx), "snb_sync")
+        self._check(self.lib.snb_set_camera_ex(self.ctx, None), "snb_set_camera_ex")
+        self.smoothed_camera = end_cam
         return out.reshape(height, width, 4).cpu().numpy()
 
     def counters(self):
@@ -187,6 +278,25 @@ class Testbed:
 
     def launch_count(self):
         return int(self.lib.snb_launch_count(self.ctx))
+
+
+def camera_path_from_keyframes(cameras):
+    """Piecewise path through camera matrices: t in [0, 1] -> camera_log_lerp between the two neighbouring keyframes (the constant-speed
+    stand-in for the reference's CameraPath spline, src/camera_path.cu, whose editor is GUI state)."""
+    cams = [np.asarray(c, np.float32).reshape(4, 3) for c in cameras]
+    lib = _lib.load()
+
+    def path(t):
+        if len(cams) == 1:
+            return cams[0]
+        x = min(max(float(t), 0.0), 1.0) * (len(cams) - 1)
+        i = min(int(x), len(cams) - 2)
+        out = np.zeros(12, np.float32)
+        a = np.ascontiguousarray(cams[i]).reshape(-1); b = np.ascontiguousarray(cams[i + 1]).reshape(-1)
+        if lib.snb_camera_log_lerp(_fp(a), _fp(b), x - i, _fp(out)) != 0:
+            raise _lib.SnbError("snb_camera_log_lerp failed")
+        return out.reshape(4, 3)
+    return path
 
 
 class Engine:

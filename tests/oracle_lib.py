@@ -5,7 +5,7 @@ import subprocess
 
 import numpy as np
 
-from synerfgine_b200._lib import Light, Material, ModelDesc, Object, RtParams, View
+from synerfgine_b200._lib import CameraEx, Light, Material, ModelDesc, Object, RtParams, View
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
@@ -38,6 +38,8 @@ def load():
         "orc_march_to_occupied": (f32, [M, pf, pf, f32]),
         "orc_init_ray": (None, [V, M, u32, u32, pf]),
         "orc_set_grid_scales": (None, [pf, u32]),
+        "orc_set_camera_ex": (None, [C.POINTER(CameraEx)]),
+        "orc_set_envmap": (None, [pf, C.c_int32, C.c_int32]),
         "orc_n_params": (u64, [u32, u32, u32, u32, f32]),
         "orc_grid_layout": (None, [u32, u32, u32, u32, f32, pf, pu32, pu32]),
         "orc_network_inference": (None, [M, pf, u64, pu16, pu16, pu32]),
@@ -67,6 +69,17 @@ def load():
 
 def P(a, t=pf):
     return a.ctypes.data_as(t)
+
+
+def set_camera_ex(ex=None, envmap=None):
+    """Stock-path camera extras of the following oracle renders (None, None: pinhole, no environment map)."""
+    lib = load()
+    lib.orc_set_camera_ex(C.byref(ex) if ex is not None else None)
+    if envmap is None:
+        lib.orc_set_envmap(None, 0, 0)
+    else:
+        e = np.ascontiguousarray(envmap, np.float32)
+        lib.orc_set_envmap(P(e), e.shape[1], e.shape[0])
 
 
 def render_nerf(model_desc, view, alt, render_mode=1, steps_per_batch=8, positions=False):

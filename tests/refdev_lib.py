@@ -74,6 +74,8 @@ def load():
         "refdev_engine_read": (C.c_int, [vp, C.c_int, pf]),
         "refdev_engine_last_n_hit": (u32, [vp]),
         "refdev_init_rays": (C.c_int, [vp, C.POINTER(RefView), C.c_int, C.c_int, pf]),
+        "refdev_init_rays_ex": (C.c_int, [vp, C.POINTER(RefView), C.c_int, C.c_int, vp, pf]),
+        "refdev_engine_set_camera_ex": (C.c_int, [vp, vp, pf, C.c_int, C.c_int]),
         "refdev_march_samples": (C.c_int, [vp, pf, u32, u32, pf, pu32, pf]),
         "refdev_rand_states": (C.c_int, [u32, u32, pu32, pf]),
         "refdev_trace_rays": (C.c_int, [vp, pf, u32, pi32, pi32, pf]),
@@ -149,9 +151,13 @@ class Model:
             raise RuntimeError("refdev_time_network: " + load().refdev_last_error().decode())
         return ms
 
-    def init_rays(self, view, w, h):
+    def init_rays(self, view, w, h, ex=None):
+        """Payloads after init_rays_from_camera: n x {origin3, dir3, t, alive}. view: RefView; ex: synerfgine_b200._lib.CameraEx (same layout) or None."""
         out = np.zeros((w * h, 8), np.float32)
-        _check(load().refdev_init_rays(self.h, C.byref(view), w, h, P(out)))
+        if ex is None:
+            _check(load().refdev_init_rays(self.h, C.byref(view), w, h, P(out)))
+        else:
+            _check(load().refdev_init_rays_ex(self.h, C.byref(view), w, h, C.byref(ex), P(out)))
         return out
 
     def march_samples(self, rays7, n_steps):
@@ -255,6 +261,12 @@ class Engine:
         _check(load().refdev_render_nerf(self.h_, model.h, scene.h if scene is not None else None, C.byref(rv), C.byref(rr) if rr is not None else None,
                                          int(alt), render_mode, C.byref(ms)))
         return ms.value
+
+    def set_camera_ex(self, ex=None, envmap=None):
+        """Camera extras (CameraEx or None) and environment map (float32 [h, w, 4] or None) of the following stock-path renders."""
+        e = np.ascontiguousarray(envmap, np.float32) if envmap is not None else None
+        _check(load().refdev_engine_set_camera_ex(self.h_, C.byref(ex) if ex is not None else None, P(e) if e is not None else None,
+                                                  e.shape[1] if e is not None else 0, e.shape[0] if e is not None else 0))
 
     def read(self, name):
         which, ch, syn = self.BUFS[name]

@@ -32,7 +32,9 @@ def set_model(snb, ctx, m):
 
 
 def dev(shape, dtype):
-    return torch.zeros(shape, dtype=dtype, device="cuda")
+    t = torch.zeros(shape, dtype=dtype, device="cuda")
+    torch.cuda.synchronize()   # the fill runs on torch's stream, the context renders on its own: finish the fill first
+    return t
 
 
 MARCHES = ["lane", "ws"]   # march kernels selectable with snb_set_option(ctx, "march", ...); the first one is the default

@@ -50,7 +50,9 @@ def ctx(snb):
 
 
 def dev(shape, dtype=None):
-    return torch.zeros(shape, dtype=dtype or torch.float32, device="cuda")
+    t = torch.zeros(shape, dtype=dtype or torch.float32, device="cuda")
+    torch.cuda.synchronize()   # the fill runs on torch's stream, the context renders on its own: finish the fill first
+    return t
 
 
 def sample_coords(n, seed=5):
@@ -320,6 +322,66 @@ def test_stock_render_nerf_against_the_reference_build(R, snb, ctx, kind, w, h):
     REPORT[f"stock_nerf_{kind}_{w}x{h}"] = rep
     assert rep["coverage"] > 0.03
     assert rep["psnr_db"] >= 50.0 and rep["pixels_over_1e-2"] <= max(2, int(5e-4 * w * h)), rep
+
+
+@pytest.mark.parametrize("case", ["dof", "motion_blur", "rolling_shutter", "parallax_near", "opencv", "opencv_fisheye", "ftheta", "latlong", "equirectangular", "everything"])
+def test_camera_extras_rays_against_the_reference_build(R, snb, ctx, case):
+    """uv_to_ray's lens / aperture / parallax / near-plane / rolling-shutter branches as the reference's own
+    init_rays_with_payload_kernel_nerf evaluates them (fast-math build) vs the product's ray set-up: origins and directions to 2e-5."""
+    m = common.model("small16x2")
+    d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
+    w, h = 64, 48
+    v = common.make_view(w, h, spp=3, snap=0)
+    ex = common.camera_ex_cases(w, h)[case]
+    rm = R.Model(m)
+    rays = rm.init_rays(R.ref_view(v), w, h, ex)
+    rm.close()
+    n = w * h
+    t, dt, cell, cnt, od = dev((n, 1)), dev((n, 1)), dev((n, 1), torch.int32), dev((n,), torch.int32), dev((n, 6))
+    assert snb.snb_set_camera_ex(ctx, C.byref(ex)) == 0
+    try:
+        assert snb.snb_march_trace(ctx, C.byref(v), 1, t.data_ptr(), dt.data_ptr(), cell.data_ptr(), cnt.data_ptr(), od.data_ptr()) == 0 and snb.snb_sync(ctx) == 0
+    finally:
+        assert snb.snb_set_camera_ex(ctx, None) == 0
+    od = od.cpu().numpy()
+    valid = np.abs(od[:, 3:]).sum(-1) > 0          # an invalid ray (f-theta beyond 90 degrees) leaves the reference's payload.dir unwritten
+    assert valid.mean() > 0.5 and (case != "ftheta" or not valid.all())
+    np.testing.assert_array_equal(rays[~valid, :3], 0.0)
+    od, rays = od[valid], rays[valid]
+    err = np.abs(od - rays[:, :6])
+    REPORT[f"camera_ex_rays_{case}"] = {"max_abs_err_origin": float(err[:, :3].max()), "max_abs_err_dir": float(err[:, 3:].max())}
+    np.testing.assert_allclose(od, rays[:, :6], rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("case,envmap", [("dof", False), ("motion_blur", True), ("everything", True), ("latlong", True)])
+def test_stock_render_with_camera_extras_against_the_reference_build(R, snb, ctx, case, envmap):
+    """Testbed::render_nerf with DoF / motion blur / lens / environment map (stock path: init_rays_from_camera with the extras, trace with
+    camera_matrix1, shade_kernel_nerf over the envmap) by the reference's build vs snb_render_nerf."""
+    kind, w, h = "fox16x2", 256, 256
+    m = common.model(kind)
+    d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
+    v = common.make_view(w, h, spp=1, snap=0)
+    ex = common.camera_ex_cases(w, h)[case]
+    env = common.test_envmap() if envmap else None
+    rm = R.Model(m); eng = R.Engine(w, h)
+    eng.set_camera_ex(ex, env)
+    eng.render_nerf(rm, v, alt=False)
+    rfb, rdepth = eng.read("nerf_rgba"), eng.read("nerf_depth")
+    eng.close(); rm.close()
+    fb, depth = dev((h, w, 4)), dev((h, w))
+    assert snb.snb_set_camera_ex(ctx, C.byref(ex)) == 0
+    assert snb.snb_set_envmap(ctx, O.P(env) if envmap else None, env.shape[1] if envmap else 0, env.shape[0] if envmap else 0) == 0
+    try:
+        assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0 and snb.snb_sync(ctx) == 0
+    finally:
+        assert snb.snb_set_camera_ex(ctx, None) == 0 and snb.snb_set_envmap(ctx, None, 0, 0) == 0
+    fb = fb.cpu().numpy()
+    err = np.abs(fb - rfb)
+    rep = {"psnr_db": common.psnr(fb, rfb), "max_abs_err": float(err.max()), "pixels_over_1e-2": int((err.max(-1) > 1e-2).sum()), "pixels": w * h,
+           "depth_over_0.05_fraction": float((np.abs(depth.cpu().numpy() - rdepth) > 0.05).mean())}
+    REPORT[f"stock_nerf_extras_{case}{'_envmap' if envmap else ''}"] = rep
+    assert rep["psnr_db"] >= 50.0 and rep["pixels_over_1e-2"] <= max(2, int(1e-3 * w * h)), rep
+    assert rep["depth_over_0.05_fraction"] < 5e-3, rep
 
 
 @pytest.mark.parametrize("name,kind,w,h,K", [("c2", "small16x2", 96, 64, 1), ("c2", "fox16x2", 480, 270, 1), ("c3", "fox16x2", 240, 135, 1), ("c2", "fox16x2", 480, 270, 4),

@@ -33,7 +33,9 @@ def load_scene(snb, ctx, name):
 
 
 def dev(shape, dtype=None):
-    return torch.zeros(shape, dtype=dtype or torch.float32, device="cuda")
+    t = torch.zeros(shape, dtype=dtype or torch.float32, device="cuda")
+    torch.cuda.synchronize()   # the fill runs on torch's stream, the context renders on its own: finish the fill first
+    return t
 
 
 def test_xorwow_matches_curand(snb, orc, ctx):
