@@ -290,6 +290,18 @@ int snb_camera_log_lerp(const float* a12, const float* b12, float t, float* out1
 int snb_scene_advance(snb_scene* s);
 /* ≙ TriangleBvhWithBranchingFactor<2>::build (src/triangle_bvh.cu:615-718); reorders tris in place. */
 int snb_bvh_build(float* tris, int32_t n_tris, int32_t prims_per_leaf, float* nodes_out, int32_t nodes_cap, int32_t* n_nodes_out);
+/* The same product built on the DEVICE: a linear BVH (Morton sort + radix tree over clusters of prims_per_leaf triangles +
+ * bottom-up bounds) in the node format above, for arrays the caller owns. tris_dev n x 9 -> tris_out_dev (Morton order, must not alias),
+ * nodes_out_dev (2 * ceil(n / prims_per_leaf) - 1 nodes of 8 floats), order_out_dev (source index of each output triangle, or NULL).
+ * max_depth_out (or NULL; giving it synchronises) = depth of the deepest leaf: the traversal stack holds 32 entries. Triangle ids differ
+ * from the host builder's, closest distances do not. snb_set_option(ctx, "bvh", "lbvh") makes snb_set_scene build this way. */
+int snb_bvh_build_dev(snb_ctx* ctx, const float* tris_dev, int32_t n_tris, int32_t prims_per_leaf, float* tris_out_dev, float* nodes_out_dev, int32_t nodes_cap,
+                      int32_t* order_out_dev, int32_t* n_nodes_out, int32_t* max_depth_out);
+/* Bounds of every node recomputed bottom-up from the triangles as they are now (vertex animation); topology and ids stay. Works on any
+ * tree in the node format, host-built ones included. */
+int snb_bvh_refit_dev(snb_ctx* ctx, const float* tris_dev, float* nodes_dev, int32_t n_nodes);
+/* Deforming mesh of the current scene: new vertices of object `index` (n_tris x 9 floats, in the order snb_set_scene received them), then refit. */
+int snb_update_object_triangles(snb_ctx* ctx, uint32_t index, const float* tris_host);
 /* ≙ tinyobj::LoadObj as used by VirtualObject (src/synerfgine/virtual_object.cu:38-75): triangles n x 9. */
 int snb_obj_load(const char* path, float* tris_out, int32_t tris_cap, int32_t* n_tris_out);
 /* ≙ grid_to_bitfield + bitfield_max_pool (src/testbed_nerf.cu:285-332,3212-3229), device kernels. density: fp32

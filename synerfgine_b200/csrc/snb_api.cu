@@ -48,6 +48,14 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		if (v == "lane") c->march_variant = 3;
 		else if (v == "ws") c->march_variant = 6;
 		else return c->fail(SNB_ERR_ARG, "march: expected ws | lane");
+	} else if (k == "bvh") {
+		if (v == "reference" || v == "host") c->bvh_builder = 0;
+		else if (v == "lbvh") c->bvh_builder = 1;
+		else return c->fail(SNB_ERR_ARG, "bvh: expected reference | lbvh");
+	} else if (k == "bvh_leaf") {
+		const int b = atoi(v.c_str());
+		if (b < 1 || b > 64) return c->fail(SNB_ERR_ARG, "bvh_leaf: expected 1..64");
+		c->bvh_leaf = b;
 	} else if (k == "alt_schedule") {
 		if (v == "auto") c->alt_mode = 0;
 		else if (v == "external") c->alt_mode = 1;
@@ -99,7 +107,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
 	// SNB_<OPTION> in the environment sets the default of snb_set_option(ctx, "<option>", ...) (A/B runs without touching the caller)
-	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch"};
+	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch", "bvh", "bvh_leaf"};
 	for (const char* opt : kEnvOptions) {
 		std::string env = std::string("SNB_") + opt;
 		for (char& ch : env) ch = (char)toupper((unsigned char)ch);
@@ -121,9 +129,10 @@ void snb_destroy(snb_ctx* c) {
 	cudaStreamSynchronize(c->stream);
 	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_present, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
 	                  &c->d_counters, &c->d_alt, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
-	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth, &c->d_envmap};
+	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth, &c->d_envmap, &c->d_tris_in, &c->d_bvh_depth, &c->lbvh.keys, &c->lbvh.keys_sorted, &c->lbvh.sort_tmp,
+	                  &c->lbvh.islot, &c->lbvh.parent, &c->lbvh.flags, &c->lbvh.bounds};
 	for (DevBuf* b : bufs) b->release();
-	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); o.order.release(); }
 	if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
@@ -256,23 +265,55 @@ static int upload_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_o
 	return SNB_OK;
 }
 
+static int check_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials, const snb_light* lights, uint32_t n_lights) {
+	if ((n_objects && !objects) || (n_materials && !materials) || (n_lights && !lights)) return c->fail(SNB_ERR_ARG, "scene arrays missing");
+	for (uint32_t i = 0; i < n_objects; ++i) {
+		if (objects[i].mat_id < 0 || (uint32_t)objects[i].mat_id >= n_materials) return c->fail(SNB_ERR_ARG, "object material index out of range");
+		if (!(objects[i].scale != 0.0f)) return c->fail(SNB_ERR_ARG, "object scale must not be 0");
+	}
+	return SNB_OK;
+}
+
 int snb_set_scene(snb_ctx* c, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
                   const snb_light* lights, uint32_t n_lights) {
-	if (!c || (n_objects && !objects) || (n_materials && !materials) || (n_lights && !lights)) return SNB_ERR_ARG;
+	if (!c) return SNB_ERR_ARG;
+	int rc = check_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights); if (rc) return rc;
 	SNB_CUDA(c, cudaSetDevice(c->device));
+	const bool device_build = c->bvh_builder == 1;
 	for (uint32_t i = 0; i < n_objects; ++i) {
-		if (!objects[i].nodes || !objects[i].tris || objects[i].n_nodes <= 0 || objects[i].n_tris <= 0) return c->fail(SNB_ERR_ARG, "object without BVH nodes or triangles");
-		if (objects[i].mat_id < 0 || (uint32_t)objects[i].mat_id >= n_materials) return c->fail(SNB_ERR_ARG, "object material index out of range");
+		if (!objects[i].tris || objects[i].n_tris <= 0) return c->fail(SNB_ERR_ARG, "object without triangles");
+		if (!device_build && (!objects[i].nodes || objects[i].n_nodes <= 0)) return c->fail(SNB_ERR_ARG, "object without BVH nodes (pass them, or set option bvh=lbvh to build on the device)");
 	}
-	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); }
+	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); o.order.release(); }
 	c->obj_store.assign(n_objects, ObjectStore());
+	if (device_build) { SNB_CUDA(c, c->d_bvh_depth.reserve(4)); SNB_CUDA(c, cudaMemsetAsync(c->d_bvh_depth.p, 0, 4, c->stream)); }
 	for (uint32_t i = 0; i < n_objects; ++i) {
 		ObjectStore& s = c->obj_store[i];
-		s.n_nodes = objects[i].n_nodes; s.n_tris = objects[i].n_tris;
-		SNB_CUDA(c, s.nodes.reserve((size_t)s.n_nodes * 32));
+		s.n_tris = objects[i].n_tris;
 		SNB_CUDA(c, s.tris.reserve((size_t)s.n_tris * 36));
-		SNB_CUDA(c, cudaMemcpyAsync(s.nodes.p, objects[i].nodes, (size_t)s.n_nodes * 32, cudaMemcpyHostToDevice, c->stream));
-		SNB_CUDA(c, cudaMemcpyAsync(s.tris.p, objects[i].tris, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+		if (!device_build) {
+			s.n_nodes = objects[i].n_nodes;
+			SNB_CUDA(c, s.nodes.reserve((size_t)s.n_nodes * 32));
+			SNB_CUDA(c, cudaMemcpyAsync(s.nodes.p, objects[i].nodes, (size_t)s.n_nodes * 32, cudaMemcpyHostToDevice, c->stream));
+			SNB_CUDA(c, cudaMemcpyAsync(s.tris.p, objects[i].tris, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+		} else {
+			// linear BVH on the device (snb_bvh_dev.cuh): triangles go up in the caller's order, come out in Morton order with `order` kept
+			s.n_nodes = lbvh_node_count(s.n_tris, c->bvh_leaf);
+			SNB_CUDA(c, s.nodes.reserve((size_t)s.n_nodes * 32));
+			SNB_CUDA(c, s.order.reserve((size_t)s.n_tris * 4));
+			SNB_CUDA(c, c->d_tris_in.reserve((size_t)s.n_tris * 36));
+			SNB_CUDA(c, cudaMemcpyAsync(c->d_tris_in.p, objects[i].tris, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+			int launches = 0;
+			SNB_CUDA(c, lbvh_build_device(c->lbvh, c->stream, c->d_tris_in.as<float>(), s.n_tris, c->bvh_leaf, s.tris.as<float>(), s.nodes.as<float>(), s.order.as<int>(),
+			                              c->d_bvh_depth.as<int>(), &launches));
+			c->launches += (uint64_t)launches;
+			s.permuted = true;
+		}
+	}
+	if (device_build && n_objects) {
+		SNB_CUDA(c, cudaMemcpyAsync(&c->bvh_max_depth, c->d_bvh_depth.p, 4, cudaMemcpyDeviceToHost, c->stream));
+		SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+		if (c->bvh_max_depth > 31) return c->fail(SNB_ERR_STATE, "device-built BVH deeper than the traversal stack (32): raise bvh_leaf");
 	}
 	return upload_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights);
 }
@@ -281,8 +322,56 @@ int snb_update_scene(snb_ctx* c, const snb_object* objects, uint32_t n_objects, 
                      const snb_light* lights, uint32_t n_lights) {
 	if (!c) return SNB_ERR_ARG;
 	if (n_objects != c->obj_store.size()) return c->fail(SNB_ERR_STATE, "snb_update_scene: object count differs from snb_set_scene");
+	int rc = check_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights); if (rc) return rc;
 	SNB_CUDA(c, cudaSetDevice(c->device));
 	return upload_scene_pods(c, objects, n_objects, materials, n_materials, lights, n_lights);
+}
+
+// Deforming mesh: new vertex positions of object `index` (n_tris x 9 floats in the order snb_set_scene received them), then a bottom-up
+// refit of its BVH bounds on the device. Topology (and with it every triangle id) stays.
+int snb_update_object_triangles(snb_ctx* c, uint32_t index, const float* tris_host) {
+	if (!c || !tris_host) return SNB_ERR_ARG;
+	if (index >= c->obj_store.size()) return c->fail(SNB_ERR_ARG, "object index out of range");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	ObjectStore& s = c->obj_store[index];
+	if (s.permuted) {
+		SNB_CUDA(c, c->d_tris_in.reserve((size_t)s.n_tris * 36));
+		SNB_CUDA(c, cudaMemcpyAsync(c->d_tris_in.p, tris_host, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+		k_gather_tris<<<(int)(((long long)s.n_tris * 9 + 255) / 256), 256, 0, c->stream>>>(c->d_tris_in.as<float>(), s.order.as<int>(), s.n_tris, s.tris.as<float>());
+		SNB_LAUNCHED(c);
+	} else SNB_CUDA(c, cudaMemcpyAsync(s.tris.p, tris_host, (size_t)s.n_tris * 36, cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, bvh_refit_device(c->lbvh, c->stream, s.tris.as<float>(), s.nodes.as<float>(), s.n_nodes));
+	c->launches += 2;
+	c->syn_reset = true;
+	return SNB_OK;
+}
+
+// ≙ TriangleBvh::build on the device, for arrays the caller owns: tris_dev (n x 9) -> tris_out_dev (Morton order), nodes_out_dev
+// ((2 * ceil(n / prims_per_leaf) - 1) x 8 floats), order_out_dev (n ints or NULL). Synchronises when max_depth_out is given.
+int snb_bvh_build_dev(snb_ctx* c, const float* tris_dev, int32_t n_tris, int32_t prims_per_leaf, float* tris_out_dev, float* nodes_out_dev, int32_t nodes_cap,
+                      int32_t* order_out_dev, int32_t* n_nodes_out, int32_t* max_depth_out) {
+	if (!c || !tris_dev || !tris_out_dev || !nodes_out_dev || n_tris <= 0 || prims_per_leaf <= 0 || tris_dev == tris_out_dev) return SNB_ERR_ARG;
+	const int n_nodes = lbvh_node_count(n_tris, prims_per_leaf);
+	if (n_nodes_out) *n_nodes_out = n_nodes;
+	if (nodes_cap < n_nodes) return c->fail(SNB_ERR_ARG, "node buffer too small");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	if (max_depth_out) { SNB_CUDA(c, c->d_bvh_depth.reserve(4)); SNB_CUDA(c, cudaMemsetAsync(c->d_bvh_depth.p, 0, 4, c->stream)); }
+	int launches = 0;
+	SNB_CUDA(c, lbvh_build_device(c->lbvh, c->stream, tris_dev, n_tris, prims_per_leaf, tris_out_dev, nodes_out_dev, order_out_dev, max_depth_out ? c->d_bvh_depth.as<int>() : nullptr, &launches));
+	c->launches += (uint64_t)launches;
+	if (max_depth_out) {
+		SNB_CUDA(c, cudaMemcpyAsync(max_depth_out, c->d_bvh_depth.p, 4, cudaMemcpyDeviceToHost, c->stream));
+		SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	}
+	return SNB_OK;
+}
+
+int snb_bvh_refit_dev(snb_ctx* c, const float* tris_dev, float* nodes_dev, int32_t n_nodes) {
+	if (!c || !tris_dev || !nodes_dev || n_nodes <= 0) return SNB_ERR_ARG;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, bvh_refit_device(c->lbvh, c->stream, tris_dev, nodes_dev, n_nodes));
+	c->launches += 2;
+	return SNB_OK;
 }
 
 int snb_seed_rng(snb_ctx* c, uint64_t seed) {

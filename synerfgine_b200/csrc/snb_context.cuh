@@ -33,9 +33,11 @@ struct DevBuf {
 	template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
-struct ObjectStore { DevBuf nodes, tris; int n_nodes = 0, n_tris = 0; };
+struct ObjectStore { DevBuf nodes, tris, order; int n_nodes = 0, n_tris = 0; bool permuted = false; };   // order: source index of every device triangle (device-built BVHs)
 
 } // namespace snb
+
+#include "snb_bvh_dev.cuh"   // needs DevBuf
 
 struct snb_ctx {
 	int device = 0;
@@ -77,6 +79,12 @@ struct snb_ctx {
 	int alt_batch = 8;                 // batch length of alt_mode 2
 	uint32_t alt_target_queries = 2u * 1024u * 1024u;   // target_n_queries of trace_alt (src/testbed_nerf.cu:2188)
 	snb::DevBuf d_alt;
+	// BVH construction (option "bvh"): 0 = the nodes the caller passes (reference builder, parity mode), 1 = linear BVH built on the device
+	int bvh_builder = 0;
+	int bvh_leaf = 4;                  // triangles per leaf of the device builder ("primitives-per-leaf" default, src/synerfgine/virtual_object.cu:14)
+	int bvh_max_depth = 0;             // deepest leaf of the last device builds (the traversal stack holds 32 entries)
+	snb::LbvhScratch lbvh;
+	snb::DevBuf d_tris_in, d_bvh_depth;
 	// stock-path camera extras (snb_set_camera_ex / snb_set_envmap); cam_ex.enabled == 0 and no envmap: plain pinhole ray generation
 	snb::CameraEx cam_ex = {};
 	bool has_cam_ex = false;

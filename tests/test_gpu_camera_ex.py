@@ -122,7 +122,7 @@ def test_stock_frame_with_extras_matches_oracle(snb, orc, ctx, case, envmap):
     if case == "slice_plane":
         assert np.allclose(depth, 1.2) and (fb[..., :3] == 0).all() if not envmap else np.allclose(depth, 1.2)
     else:
-        assert (rfb[..., 3] > 0.5).mean() > 0.03
+        assert (rfb[..., 3] > 0.5).mean() > (0.01 if case == "latlong" else 0.03)     # the panorama shows the scene small
     if envmap and case != "slice_plane":
         assert (fb[..., 3] > 0.99).all()         # every valid ray sees the map behind the NeRF
 
