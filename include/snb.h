@@ -300,6 +300,13 @@ int snb_bvh_build_dev(snb_ctx* ctx, const float* tris_dev, int32_t n_tris, int32
 /* Bounds of every node recomputed bottom-up from the triangles as they are now (vertex animation); topology and ids stay. Works on any
  * tree in the node format, host-built ones included. */
 int snb_bvh_refit_dev(snb_ctx* ctx, const float* tris_dev, float* nodes_dev, int32_t n_nodes);
+/* Allocation-free variant of snb_bvh_refit_dev. NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same inputs, outputs and result as
+ * snb_bvh_refit_dev, but the scratch (8 B per node) lives in a fixed device array inside the library (2 MiB per GPU, held until exit), so the
+ * call allocates and frees nothing. n_nodes > SNB_REFIT_NOALLOC_MAX_NODES is rejected with SNB_ERR_ARG and a message. All calls on a GPU
+ * share that one array: calls whose kernels overlap on the GPU (different streams / contexts) race; serialise them. */
+#define SNB_REFIT_NOALLOC_MAX_NODES 262144
+int snb_bvh_refit_dev_noalloc(snb_ctx* ctx, const float* tris_dev, float* nodes_dev, int32_t n_nodes);
 /* Deforming mesh of the current scene: new vertices of object `index` (n_tris x 9 floats, in the order snb_set_scene received them), then refit. */
 int snb_update_object_triangles(snb_ctx* ctx, uint32_t index, const float* tris_host);
 /* ≙ tinyobj::LoadObj as used by VirtualObject (src/synerfgine/virtual_object.cu:38-75): triangles n x 9. */

@@ -102,6 +102,7 @@ SIGNATURES = {
     "snb_set_alt_schedule": (C.c_int, [vp, C.POINTER(u8), u32]),
     "snb_bvh_build_dev": (C.c_int, [vp, vp, i32, i32, vp, vp, i32, vp, C.POINTER(i32), C.POINTER(i32)]),
     "snb_bvh_refit_dev": (C.c_int, [vp, vp, vp, i32]),
+    "snb_bvh_refit_dev_noalloc": (C.c_int, [vp, vp, vp, i32]),
     "snb_update_object_triangles": (C.c_int, [vp, u32, pf32]),
     "snb_set_camera_ex": (C.c_int, [vp, C.POINTER(CameraEx)]),
     "snb_set_envmap": (C.c_int, [vp, pf32, i32, i32]),

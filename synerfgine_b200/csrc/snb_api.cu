@@ -388,6 +388,47 @@ int snb_reset_accumulation(snb_ctx* c) {
 
 } // extern "C"
 
+// ---- allocation-free refit (no counterpart in the reference) -----------------------------
+// Some callers cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). snb_bvh_refit_dev keeps its
+// scratch (parent index + arrival counter per node) in grow-only context buffers; this variant keeps it in a fixed array in device memory
+// instead. Every GPU that loads the library holds the array (SNB_REFIT_NOALLOC_MAX_NODES x 8 B = 2 MiB) until the process exits.
+static __device__ __align__(256) unsigned int g_refit_noalloc_scratch[2 * SNB_REFIT_NOALLOC_MAX_NODES];   // [0, MAX): parent, [MAX, 2 MAX): arrival flags
+
+#include <mutex>
+static const int kNoAllocMaxDevices = 64;
+static std::mutex g_refit_noalloc_mutex;
+static unsigned int* g_refit_noalloc_ptr[kNoAllocMaxDevices] = {};   // device address of the array, looked up once per device
+
+extern "C" int snb_bvh_refit_dev_noalloc(snb_ctx* c, const float* tris_dev, float* nodes_dev, int32_t n_nodes) {
+	if (!c || !tris_dev || !nodes_dev || n_nodes <= 0) return SNB_ERR_ARG;
+	if (n_nodes > SNB_REFIT_NOALLOC_MAX_NODES) {
+		char msg[160];
+		snprintf(msg, sizeof msg, "snb_bvh_refit_dev_noalloc: %d nodes exceed the fixed scratch of %d nodes (use snb_bvh_refit_dev)", (int)n_nodes, (int)SNB_REFIT_NOALLOC_MAX_NODES);
+		return c->fail(SNB_ERR_ARG, msg);
+	}
+	if (c->device < 0 || c->device >= kNoAllocMaxDevices) return c->fail(SNB_ERR_ARG, "snb_bvh_refit_dev_noalloc: device ordinal out of range");
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	unsigned int* scratch = nullptr;
+	{
+		// In host code `g_refit_noalloc_scratch` is only a handle: the device address comes from the runtime, once per device, with that device current.
+		std::lock_guard<std::mutex> lock(g_refit_noalloc_mutex);
+		if (!g_refit_noalloc_ptr[c->device]) {
+			void* p = nullptr;
+			SNB_CUDA(c, cudaGetSymbolAddress(&p, g_refit_noalloc_scratch));
+			g_refit_noalloc_ptr[c->device] = static_cast<unsigned int*>(p);
+		}
+		scratch = g_refit_noalloc_ptr[c->device];
+	}
+	int* parent = reinterpret_cast<int*>(scratch);
+	unsigned int* flags = scratch + SNB_REFIT_NOALLOC_MAX_NODES;
+	const int blocks = (n_nodes + 255) / 256;
+	k_bvh_parents<<<blocks, 256, 0, c->stream>>>(nodes_dev, n_nodes, parent, flags);   // also clears the arrival flags of [0, n_nodes): the array keeps the last call's contents
+	SNB_LAUNCHED(c);
+	k_bvh_fit<<<blocks, 256, 0, c->stream>>>(nodes_dev, n_nodes, tris_dev, parent, flags);
+	SNB_LAUNCHED(c);
+	return SNB_OK;
+}
+
 #include "snb_render.inl"
 #include "snb_taps.inl"
 #include "snb_present.inl"
