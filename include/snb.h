@@ -197,6 +197,10 @@ int snb_set_alt_schedule(snb_ctx* ctx, const uint8_t* steps_host, uint32_t n /* 
 /* ---- inputs ------------------------------------------------------------------------------------------- */
 /* ≙ Testbed::load_snapshot result handed over as arrays (src/testbed.cu:4878-4992). */
 int snb_set_model(snb_ctx* ctx, const snb_model_desc* model);
+/* The same with model->params and model->bitfield in DEVICE memory of the context's GPU — the state the reference holds after training or
+ * load_snapshot (tcnn's params buffer, Testbed::Nerf::density_grid_bitfield; SURVEY.md 8b "no hidden host copies"): hash table and bitfield
+ * are copied device to device, only the 20 KB of MLP weights are read back to be laid out in fragment order. */
+int snb_set_model_dev(snb_ctx* ctx, const snb_model_desc* model);
 /* ≙ Engine::set_virtual_world after parsing (src/synerfgine/engine.cu:21-78): uploads world, materials, lights. */
 int snb_set_scene(snb_ctx* ctx, const snb_object* objects, uint32_t n_objects, const snb_material* materials, uint32_t n_materials,
                   const snb_light* lights, uint32_t n_lights);

@@ -78,6 +78,7 @@ SIGNATURES = {
     "snb_version": (C.c_char_p, []),
     "snb_set_option": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
     "snb_set_model": (C.c_int, [vp, C.POINTER(ModelDesc)]),
+    "snb_set_model_dev": (C.c_int, [vp, C.POINTER(ModelDesc)]),
     "snb_set_scene": (C.c_int, [vp, C.POINTER(Object), u32, C.POINTER(Material), u32, C.POINTER(Light), u32]),
     "snb_update_scene": (C.c_int, [vp, C.POINTER(Object), u32, C.POINTER(Material), u32, C.POINTER(Light), u32]),
     "snb_seed_rng": (C.c_int, [vp, u64]),

@@ -147,9 +147,24 @@ int snb_sync(snb_ctx* c) {
 	return SNB_OK;
 }
 
-int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
+static int set_model_impl(snb_ctx* c, const snb_model_desc* m, bool on_device);
+int snb_set_model(snb_ctx* c, const snb_model_desc* m) { return set_model_impl(c, m, false); }
+// The same with `params` and `bitfield` pointing to DEVICE memory of the context's GPU (a model that was just trained or loaded there):
+// the hash table and the bitfield are copied device-to-device; only the 20 KB of MLP weights visit the host, to be laid out in fragment order.
+int snb_set_model_dev(snb_ctx* c, const snb_model_desc* m) { return set_model_impl(c, m, true); }
+
+static int set_model_impl(snb_ctx* c, const snb_model_desc* m, bool on_device) {
 	if (!c || !m || !m->params) return SNB_ERR_ARG;
 	SNB_CUDA(c, cudaSetDevice(c->device));
+	const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+	std::vector<uint16_t> mlp_host;
+	const uint16_t* mlp_params = m->params;
+	if (on_device) {
+		mlp_host.resize(kMlpHalves);
+		SNB_CUDA(c, cudaMemcpyAsync(mlp_host.data(), m->params, kMlpHalves * 2, cudaMemcpyDeviceToHost, c->stream));
+		SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+		mlp_params = mlp_host.data();
+	}
 	const uint32_t F = m->n_features_per_level, L = m->n_levels;
 	if (!(F == 1 || F == 2 || F == 4 || F == 8) || L * F != (uint32_t)kFeat || L > (uint32_t)kMaxLevels)
 		return c->fail(SNB_ERR_UNSUPPORTED, "encoding must satisfy n_levels * n_features_per_level == 32 with F in {1,2,4,8}");
@@ -160,19 +175,19 @@ int snb_set_model(snb_ctx* c, const snb_model_desc* m) {
 	SNB_CUDA(c, c->d_mlp.reserve(kMlpHalves * 2));
 	SNB_CUDA(c, c->d_mlp_frag.reserve(kFragWords * 4));
 	SNB_CUDA(c, c->d_grid.reserve(n_grid * 2));
-	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp.p, m->params, kMlpHalves * 2, cudaMemcpyHostToDevice, c->stream));
-	SNB_CUDA(c, cudaMemcpyAsync(c->d_grid.p, m->params + kMlpHalves, n_grid * 2, cudaMemcpyHostToDevice, c->stream));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp.p, m->params, kMlpHalves * 2, kind, c->stream));
+	SNB_CUDA(c, cudaMemcpyAsync(c->d_grid.p, m->params + kMlpHalves, n_grid * 2, kind, c->stream));
 	std::vector<uint32_t> frag(kFragWords);
-	build_mma_fragments(m->params, frag.data());
+	build_mma_fragments(mlp_params, frag.data());
 	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp_frag.p, frag.data(), kFragWords * 4, cudaMemcpyHostToDevice, c->stream));
 	std::vector<uint16_t> umma(kMlpHalves);
-	tc::build_umma_weights(m->params, umma.data());
+	tc::build_umma_weights(mlp_params, umma.data());
 	SNB_CUDA(c, c->d_mlp_umma.reserve(kMlpHalves * 2));
 	SNB_CUDA(c, cudaMemcpyAsync(c->d_mlp_umma.p, umma.data(), kMlpHalves * 2, cudaMemcpyHostToDevice, c->stream));
 	const size_t bf_bytes = (size_t)kCascades * kGridCells / 8;
 	if (m->bitfield) {
 		SNB_CUDA(c, c->d_bitfield.reserve(bf_bytes));
-		SNB_CUDA(c, cudaMemcpyAsync(c->d_bitfield.p, m->bitfield, bf_bytes, cudaMemcpyHostToDevice, c->stream));
+		SNB_CUDA(c, cudaMemcpyAsync(c->d_bitfield.p, m->bitfield, bf_bytes, kind, c->stream));
 	}
 	{   // level scales as the device evaluates them (k_grid_scales); resolutions follow, the offset table stays the host's like tcnn's
 		DevBuf tmp;

@@ -16,6 +16,8 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 #include "../../include/snb.h"
@@ -45,8 +47,10 @@ struct Reader {
 	uint64_t be(int n) { uint64_t v = 0; for (int k = 0; k < n; ++k) v = (v << 8) | *p++; return v; }
 	bool str(size_t n, Node& o) { if (!need(n)) return false; o.kind = Node::STR; o.s.assign((const char*)p, n); p += n; return true; }
 	bool bin(size_t n, Node& o) { if (!need(n)) return false; o.kind = Node::BIN; o.bin = p; o.bin_len = n; p += n; return true; }
-	bool arr(size_t n, Node& o) { o.kind = Node::ARR; o.arr.resize(n); for (auto& e : o.arr) if (!value(e)) return false; return true; }
+	// every element takes at least one byte (a map entry two): a count beyond the remaining bytes is a malformed file, not an allocation request
+	bool arr(size_t n, Node& o) { if (!need(n)) return false; o.kind = Node::ARR; o.arr.resize(n); for (auto& e : o.arr) if (!value(e)) return false; return true; }
 	bool map(size_t n, Node& o) {
+		if (n > (size_t)(end - p) / 2) { err = "truncated msgpack"; return false; }
 		o.kind = Node::MAP; o.map.resize(n);
 		for (auto& kv : o.map) { Node k; if (!value(k)) return false; if (k.kind != Node::STR) { err = "non-string map key"; return false; } kv.first = k.s; if (!value(kv.second)) return false; }
 		return true;
@@ -180,9 +184,15 @@ static void set_err(char* err, size_t n, const std::string& s) { if (err && n) {
 
 extern "C" {
 
+static int snapshot_load_impl(const char* path, snb_snapshot** out, char* err, size_t err_len);
 int snb_snapshot_load(const char* path, snb_snapshot** out, char* err, size_t err_len) {
 	if (!path || !out) return SNB_ERR_ARG;
 	*out = nullptr;
+	try { return snapshot_load_impl(path, out, err, err_len); }     // nothing may unwind through the C boundary
+	catch (const std::bad_alloc&) { set_err(err, err_len, "out of memory while reading the snapshot"); return SNB_ERR_PARSE; }
+	catch (const std::exception& e) { set_err(err, err_len, std::string("snapshot: ") + e.what()); return SNB_ERR_PARSE; }
+}
+static int snapshot_load_impl(const char* path, snb_snapshot** out, char* err, size_t err_len) {
 	std::vector<uint8_t> file;
 	if (!read_file(path, file)) { set_err(err, err_len, std::string("cannot read ") + path); return SNB_ERR_IO; }
 	std::unique_ptr<snb_snapshot> s(new snb_snapshot());
@@ -197,10 +207,19 @@ int snb_snapshot_load(const char* path, snb_snapshot** out, char* err, size_t er
 	const Node* mode = snap->get("mode");
 	if (mode && mode->kind == Node::STR && mode->s != "nerf" && mode->s != "Nerf") { set_err(err, err_len, "snapshot mode is '" + mode->s + "', only NeRF snapshots are in scope"); return SNB_ERR_UNSUPPORTED; }
 	s->version = uval(snap->get("version"), 0);
+	if (s->version < 1) { set_err(err, err_len, "Snapshot uses an old format and can not be loaded."); return SNB_ERR_UNSUPPORTED; }   // testbed.cu:4880-4882 (SNAPSHOT_FORMAT_VERSION 1)
 	snb_model_desc& m = s->model; std::memset(&m, 0, sizeof m);
 	// ---- encoding (reset_network, testbed.cu:3705-3741) ----
 	const Node* enc = s->root.get("encoding");
 	if (!enc || enc->kind != Node::MAP) { set_err(err, err_len, "no 'encoding' object"); return SNB_ERR_PARSE; }
+	{   // the path implements tcnn's hash grid (otype HashGrid, or Grid with type Hash) and 64-wide fully fused MLPs with 1 + 2 hidden layers
+		const Node* ot = enc->get("otype"); const Node* ty = enc->get("type");
+		const std::string o = ot && ot->kind == Node::STR ? ot->s : "HashGrid", t = ty && ty->kind == Node::STR ? ty->s : "Hash";
+		if (!((o == "HashGrid") || (o == "Grid" && t == "Hash"))) { set_err(err, err_len, "encoding '" + o + "' is not supported (expected HashGrid)"); return SNB_ERR_UNSUPPORTED; }
+		const Node* net = s->root.get("network"); const Node* rgb = s->root.get("rgb_network");
+		if (net && net->kind == Node::MAP && (uval(net->get("n_neurons"), 64) != 64 || uval(net->get("n_hidden_layers"), 1) != 1)) { set_err(err, err_len, "density network must be 64 neurons x 1 hidden layer"); return SNB_ERR_UNSUPPORTED; }
+		if (rgb && rgb->kind == Node::MAP && (uval(rgb->get("n_neurons"), 64) != 64 || uval(rgb->get("n_hidden_layers"), 2) != 2)) { set_err(err, err_len, "rgb network must be 64 neurons x 2 hidden layers"); return SNB_ERR_UNSUPPORTED; }
+	}
 	m.n_features_per_level = uval(enc->get("n_features_per_level"), 2);
 	m.n_levels = enc->get("n_features") ? uval(enc->get("n_features"), 32) / std::max(1u, m.n_features_per_level) : uval(enc->get("n_levels"), 16);
 	m.log2_hashmap_size = uval(enc->get("log2_hashmap_size"), 15);
@@ -260,8 +279,23 @@ int snb_snapshot_get(const snb_snapshot* s, snb_model_desc* model, const uint16_
 
 int snb_snapshot_save(const char* path, const snb_model_desc* m, const uint16_t* density_fp16, uint64_t n_density, uint32_t aabb_scale, const float* camera12, int compress) {
 	if (!path || !m || !m->params) return SNB_ERR_ARG;
+	if (density_fp16 == nullptr) n_density = 0;
 	Writer w;
-	w.map(2);
+	auto mlp = [&](const char* name, unsigned hidden) {
+		w.key(name); w.map(5);
+		w.key("otype"); w.str("FullyFusedMLP"); w.key("activation"); w.str("ReLU"); w.key("output_activation"); w.str("None");
+		w.key("n_neurons"); w.uint(64); w.key("n_hidden_layers"); w.uint(hidden);
+	};
+	// root: the network description Testbed::reset_network reads back (configs/nerf/base.json defaults) + the snapshot object
+	w.map(7);
+	mlp("network", 1); mlp("rgb_network", 2);
+	w.key("dir_encoding"); w.map(2); w.key("otype"); w.str("Composite"); w.key("nested"); w.arr(2);
+	w.map(3); w.key("n_dims_to_encode"); w.uint(3); w.key("otype"); w.str("SphericalHarmonics"); w.key("degree"); w.uint(4);
+	w.map(1); w.key("otype"); w.str("Identity");
+	w.key("loss"); w.map(1); w.key("otype"); w.str("Huber");
+	w.key("optimizer"); w.map(3); w.key("otype"); w.str("Ema"); w.key("decay"); w.f32(0.95f); w.key("nested"); w.map(5);
+	w.key("otype"); w.str("ExponentialDecay"); w.key("decay_start"); w.uint(20000); w.key("decay_interval"); w.uint(10000); w.key("decay_base"); w.f32(0.33f); w.key("nested"); w.map(6);
+	w.key("otype"); w.str("Adam"); w.key("learning_rate"); w.f32(1e-2f); w.key("beta1"); w.f32(0.9f); w.key("beta2"); w.f32(0.99f); w.key("epsilon"); w.f32(1e-15f); w.key("l2_reg"); w.f32(1e-6f);
 	w.key("encoding"); w.map(6);
 	w.key("otype"); w.str("HashGrid");
 	w.key("n_levels"); w.uint(m->n_levels);
@@ -269,15 +303,19 @@ int snb_snapshot_save(const char* path, const snb_model_desc* m, const uint16_t*
 	w.key("log2_hashmap_size"); w.uint(m->log2_hashmap_size);
 	w.key("base_resolution"); w.uint(m->base_resolution);
 	w.key("per_level_scale"); w.f32(m->per_level_scale);
-	w.key("snapshot"); w.map(11 + (camera12 ? 1 : 0));
+	w.key("snapshot"); w.map(13 + (camera12 ? 1 : 0));
 	w.key("version"); w.uint(1);
+	w.key("training_step"); w.uint(0);      // read unconditionally by load_snapshot (testbed.cu:4972-4973)
+	w.key("loss"); w.f32(0.0f);
 	w.key("mode"); w.str("nerf");
 	w.key("n_params"); w.uint(m->n_params);
 	w.key("params_type"); w.str("__half");
 	w.key("params_binary"); w.bin(m->params, (size_t)m->n_params * 2);
 	w.key("density_grid_size"); w.uint(128);
 	w.key("density_grid_binary"); w.bin(density_fp16, density_fp16 ? (size_t)n_density * 2 : 0);
-	w.key("nerf"); w.map(3);
+	w.key("nerf"); w.map(4);
+	w.key("rgb"); w.map(3);                  // training counters, read unconditionally (testbed.cu:4901-4903); Testbed defaults (testbed.h:509-512)
+	w.key("rays_per_batch"); w.uint(1u << 12); w.key("measured_batch_size"); w.uint(0); w.key("measured_batch_size_before_compaction"); w.uint(0);
 	w.key("aabb_scale"); w.uint(aabb_scale);
 	static const char* act[] = {"None", "ReLU", "Logistic", "Exponential"};
 	w.key("rgb_activation"); w.str(act[m->rgb_activation & 3]);

@@ -17,9 +17,10 @@ passed in as a callable so the same code path is exercised on both.
 from dataclasses import dataclass
 
 
-def halo_for(nerf_shadow_kernel, show_shadow_on_nerf=True):
-    """Columns a strip must recompute beyond its own: normals stencil (2) + shadow window (k // 2) read normals -> k // 2 + 2."""
-    return max(2, (int(nerf_shadow_kernel) // 2 if show_shadow_on_nerf else 0) + 2)
+def halo_for(nerf_shadow_kernel, show_shadow_on_nerf=True, syn_px_scale=1):
+    """Columns (or rows) a strip must recompute beyond its own, in FRAME (mesh-layer) pixels: the normals stencil (2) + the shadow
+    window (k // 2) run on the NeRF layer, whose pixels are `syn_px_scale` frame pixels wide -> (k // 2 + 2) * syn_px_scale."""
+    return max(2, (int(nerf_shadow_kernel) // 2 if show_shadow_on_nerf else 0) + 2) * max(1, int(syn_px_scale))
 
 
 @dataclass(frozen=True)

@@ -391,3 +391,31 @@ def test_large_frame_4k(snb, ctx):
     t = Tile(W - 517, H - 301, 517, 301)
     pfb, pdepth, ppos, _ = _render_full(snb, ctx, v, tile=t)
     assert torch.equal(pfb, fb[t.y0:, t.x0:]) and torch.equal(pdepth, depth[t.y0:, t.x0:]) and torch.equal(ppos, pos[t.y0:, t.x0:])
+
+
+def test_set_model_from_device_memory_renders_identically(snb):
+    """snb_set_model_dev: parameters and bitfield already on the GPU (SURVEY.md 8b "no hidden host copies") -> the same frame, bit for bit."""
+    m = common.model("small16x2")
+    v = common.make_view(128, 96)
+    frames = []
+    for on_device in (False, True):
+        c = C.c_void_p(); assert snb.snb_create(0, None, C.byref(c)) == 0
+        try:
+            d = m.desc()
+            if on_device:
+                n = int(d.n_params)
+                params = torch.from_numpy(np.ctypeslib.as_array(d.params, shape=(n,)).astype(np.int16, copy=True)).cuda()
+                bits = torch.from_numpy(np.ctypeslib.as_array(d.bitfield, shape=(8 * 128 ** 3 // 8,)).copy()).cuda()
+                torch.cuda.synchronize()
+                d.params = C.cast(C.c_void_p(params.data_ptr()), C.POINTER(C.c_uint16)); d.bitfield = C.cast(C.c_void_p(bits.data_ptr()), C.POINTER(C.c_uint8))
+                assert snb.snb_set_model_dev(c, C.byref(d)) == 0, snb.snb_last_error(c)
+            else:
+                assert snb.snb_set_model(c, C.byref(d)) == 0
+            fb, depth = dev((96, 128, 4), torch.float32), dev((96, 128), torch.float32)
+            torch.cuda.synchronize()
+            assert snb.snb_render_nerf(c, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0 and snb.snb_sync(c) == 0
+            frames.append((fb.cpu().numpy(), depth.cpu().numpy()))
+        finally:
+            snb.snb_destroy(c)
+    assert frames[0][0][..., 3].max() > 0.5
+    assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])

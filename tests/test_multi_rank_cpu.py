@@ -49,6 +49,14 @@ def test_strip_alignment_to_syn_px_scale():
 
 def test_halo_and_frame_batch():
     assert tiles.halo_for(4) == 4 and tiles.halo_for(1) == 2 and tiles.halo_for(8) == 6 and tiles.halo_for(8, False) == 2
+    # the stencils run on the NeRF layer: with syn_px_scale 2 the halo doubles in frame pixels, and a strip keeps (k // 2 + 2) NeRF columns of it
+    assert tiles.halo_for(4, True, 2) == 8 and tiles.halo_for(1, True, 4) == 8
+    for world in (2, 3):
+        for r in range(world):
+            s = tiles.strip_for(r, world, 1920, tiles.halo_for(4, True, 2), align=2)
+            left, right = (s.x0 - s.hx0) // 2, (s.hx1 - s.x1) // 2              # halo in NeRF-layer columns
+            assert (left >= 4 or s.hx0 == 0) and (right >= 4 or s.hx1 == 1920)
+            assert s.hx0 % 2 == 0 and s.hx1 % 2 == 0
     got = [list(tiles.frame_batch_for(r, 8, 64)) for r in range(8)]
     assert sum(got, []) == list(range(64)) and all(len(g) == 8 for g in got)
     got = [list(tiles.frame_batch_for(r, 3, 10)) for r in range(3)]

@@ -121,6 +121,13 @@ def test_writer_round_trip_and_python_can_read_it(snb, tmp_path):
         assert tree["snapshot"]["params_binary"] == m.params.tobytes() and tree["snapshot"]["density_grid_binary"] == dens.tobytes()
         assert tree["encoding"]["n_levels"] == m.n_levels and tree["snapshot"]["nerf"]["aabb_scale"] == m.aabb_scale
         assert tree["snapshot"]["camera"]["matrix"] == rows(list(cam), 4, 3)
+        # every key Testbed::load_snapshot / reset_network reads without a default (src/testbed.cu:4878-4992): the reference can load the file
+        snap = tree["snapshot"]
+        assert snap["version"] >= 1 and snap["training_step"] == 0 and snap["loss"] == 0.0 and snap["density_grid_size"] == 128
+        assert set(snap["nerf"]["rgb"]) == {"rays_per_batch", "measured_batch_size", "measured_batch_size_before_compaction"}
+        assert tree["network"]["n_neurons"] == 64 and tree["network"]["n_hidden_layers"] == 1 and tree["rgb_network"]["n_hidden_layers"] == 2
+        assert tree["dir_encoding"]["nested"][0]["degree"] == 4 and tree["loss"]["otype"] == "Huber"
+        assert tree["optimizer"]["nested"]["nested"]["otype"] == "Adam" and tree["encoding"]["otype"] == "HashGrid"
         rc, h, err = load(snb, path)
         assert rc == 0, err
         rc, d2, dp, n, scale, got_cam = get(snb, h)
@@ -142,6 +149,12 @@ def test_malformed_files_are_rejected_with_a_message(snb, tmp_path):
         "sdf.msgpack": msgpack.packb({"encoding": {}, "snapshot": {"mode": "sdf", "params_binary": b"", "params_type": "__half"}}, use_bin_type=True),
         "float_params.msgpack": msgpack.packb({"encoding": {}, "snapshot": {"mode": "nerf", "params_type": "float", "params_binary": b"\0" * 8}}, use_bin_type=True),
         "empty.msgpack": b"",
+        # the format version is enforced, other encodings / MLP shapes are refused, a huge element count is a parse error
+        "old_version.msgpack": msgpack.packb({**msgpack.unpackb(blob, raw=False), "snapshot": {**msgpack.unpackb(blob, raw=False)["snapshot"], "version": 0}}, use_bin_type=True),
+        "dense_grid.msgpack": msgpack.packb({**msgpack.unpackb(blob, raw=False), "encoding": {**msgpack.unpackb(blob, raw=False)["encoding"], "otype": "DenseGrid"}}, use_bin_type=True),
+        "wide_mlp.msgpack": msgpack.packb({**msgpack.unpackb(blob, raw=False), "network": {"otype": "FullyFusedMLP", "n_neurons": 128, "n_hidden_layers": 1}}, use_bin_type=True),
+        "huge_array.msgpack": b"\x82\xa8encoding\xdd\xff\xff\xff\xf0\x00",
+        "huge_map.msgpack": b"\xdf\xff\xff\xff\xf0\xa1a\x00",
     }
     for name, data in cases.items():
         p = tmp_path / name
