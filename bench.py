@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--march", default="", help="ws | lane (default: the library's)")
     ap.add_argument("--alt-schedule", default="", help="auto | fixed (default: the reference's count-dependent batch lengths)")
+    ap.add_argument("--batch-assign", default="strided", choices=["strided", "contiguous"], help="c5-batch: which frames of the path a rank renders")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="240x135")
@@ -311,7 +312,11 @@ def run_ours(args, rank, local_rank, world):
     stock_fb = torch.empty((H, W, 4), device="cuda") if stock else None
     stock_depth = torch.empty((H, W), device="cuda") if stock else None
     sched_checks = {"n": 0, "changed": 0}
-    my_frames = list(tiles.frame_batch_for(rank, world, cfg["frames"])) if cfg.get("batch") else None
+    # frame batch: whole frames per rank. Frames of a camera path differ in cost (C4: p95 / mean = 1.3), so contiguous chunks leave the rank
+    # with the expensive stretch of the path as the step time; strided assignment (frame f -> rank f mod N) gives every rank the same mix.
+    my_frames = None
+    if cfg.get("batch"):
+        my_frames = set(range(rank, cfg["frames"], world)) if args.batch_assign == "strided" else set(tiles.frame_batch_for(rank, world, cfg["frames"]))
 
     def sync_alt_schedule():
         """external schedule: the counts of all bands are summed and every rank sets the sequence they imply (snb.h)."""
@@ -527,7 +532,7 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 march / f16 MLP (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": cfg["workload"], "name": args.config, "resolution": [W, H], "frames_per_step": frames_per_step, "march": tb_march,
                        "parallelism": (f"{world} row bands, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves); rgba + depth assembled on rank 0 (NCCL p2p, 20 B/px)" if split_frame
-                                       else (f"{cfg['frames']} frames sharded over {world} ranks, whole frames, no halo" if cfg.get("batch") else "single GPU")),
+                                       else (f"{cfg['frames']} frames sharded over {world} ranks ({args.batch_assign}), whole frames, no halo" if cfg.get("batch") else "single GPU")),
                        "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples_per_launch, "rays_marched_per_frame": rays_per_launch,
                        "march_stats_last_frame": march_stats, "alt_schedule": alt, "ms_per_frame": total_ms / nframes,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()},
