@@ -42,7 +42,8 @@ def parse_args():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--march", default="", help="ws | lane (default: the library's)")
     ap.add_argument("--alt-schedule", default="", help="auto | fixed (default: the reference's count-dependent batch lengths)")
-    ap.add_argument("--batch-assign", default="strided", choices=["strided", "contiguous"], help="c5-batch: which frames of the path a rank renders")
+    ap.add_argument("--batch-assign", default="contiguous", choices=["contiguous", "balanced", "strided"],
+                    help="c5-batch: which frames of the path a rank renders (balanced = contiguous chunks sized by measured per-frame cost)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="240x135")
@@ -312,11 +313,15 @@ def run_ours(args, rank, local_rank, world):
     stock_fb = torch.empty((H, W, 4), device="cuda") if stock else None
     stock_depth = torch.empty((H, W), device="cuda") if stock else None
     sched_checks = {"n": 0, "changed": 0}
-    # frame batch: whole frames per rank. Frames of a camera path differ in cost (C4: p95 / mean = 1.3), so contiguous chunks leave the rank
-    # with the expensive stretch of the path as the step time; strided assignment (frame f -> rank f mod N) gives every rank the same mix.
+    # frame batch: whole frames per rank. Frames of a camera path differ in cost (C4: p95 / mean = 1.3), so equal contiguous chunks leave the
+    # rank with the expensive stretch of the path as the step time. Strided assignment (frame f -> rank f mod N) evens the mix but makes every
+    # frame a camera jump for the batch-schedule predictor (more march passes: measured 906 against 1011 Mrays/s at N = 8). "balanced" keeps
+    # chunks contiguous and sizes them by the per-frame cost measured during warm-up (one all_reduce of a 64-float vector, control plane):
+    # measured 991. Equal contiguous chunks are the default.
     my_frames = None
     if cfg.get("batch"):
         my_frames = set(range(rank, cfg["frames"], world)) if args.batch_assign == "strided" else set(tiles.frame_batch_for(rank, world, cfg["frames"]))
+    batch_bounds = None
 
     def sync_alt_schedule():
         """external schedule: the counts of all bands are summed and every rank sets the sequence they imply (snb.h)."""
@@ -381,21 +386,36 @@ def run_ours(args, rank, local_rank, world):
         bal.tick()
         return rgba, depth
 
-    def one_step(host=None):
+    def one_step(host=None, cost=None):
         if not cfg.get("batch"):
             return render_one(host)
         for f in range(cfg["frames"]):                    # every rank walks the whole path on the host; it renders its own frames
             if f in my_frames:
+                if cost is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(stream)
                 render_one(host)
+                if cost is not None:
+                    e1.record(stream); cost.append((f, e0, e1))
             else:
-                eng.advance_camera_path()
-                if eng.enable_animations:
-                    eng.scene.advance()
+                eng.skip_frames(1)                         # host-side position only (no camera matrix, no array refresh): ~2 µs
         return None
 
     with torch.cuda.stream(stream):
         for _ in range(Wu):
             one_step()
+        if cfg.get("batch") and world > 1 and args.batch_assign == "balanced":
+            cost = []
+            one_step(cost=cost)
+            stream.synchronize()
+            vec = torch.zeros(cfg["frames"], device="cuda")
+            for f, e0, e1 in cost:
+                vec[f] = e0.elapsed_time(e1)
+            dist.all_reduce(vec)
+            batch_bounds = tiles.balanced_bounds(vec.cpu().numpy().astype(np.float64), world, 1, 1)
+            my_frames = set(range(batch_bounds[rank], batch_bounds[rank + 1]))
+            for _ in range(2):                             # settle on the new chunks (their first frames are the camera jumps now)
+                one_step()
         stream.synchronize()
         if world > 1:
             dist.barrier()
@@ -532,7 +552,7 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 march / f16 MLP (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": cfg["workload"], "name": args.config, "resolution": [W, H], "frames_per_step": frames_per_step, "march": tb_march,
                        "parallelism": (f"{world} row bands, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves); rgba + depth assembled on rank 0 (NCCL p2p, 20 B/px)" if split_frame
-                                       else (f"{cfg['frames']} frames sharded over {world} ranks ({args.batch_assign}), whole frames, no halo" if cfg.get("batch") else "single GPU")),
+                                       else (f"{cfg['frames']} frames sharded over {world} ranks ({args.batch_assign}{': chunk edges ' + str(batch_bounds) if batch_bounds else ''}), whole frames, no halo" if cfg.get("batch") else "single GPU")),
                        "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples_per_launch, "rays_marched_per_frame": rays_per_launch,
                        "march_stats_last_frame": march_stats, "alt_schedule": alt, "ms_per_frame": total_ms / nframes,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()},

@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_common.h).
 // NerfNetwork inference: hash-grid encoding -> density MLP -> SH -> rgb MLP.
-// Device-only code in the reference (tcnn); no reference test pins it: parity unpinned.
+// Device-only code in the reference (tcnn). Pinned since round 2 against the reference's own kernel_grid / kernel_mlp_fused run on the GPU
+// (oracle/_ref/libref_dev.so, tests/test_gpu_refdev.py): features bit for bit, network outputs within fp16-accumulation tolerance.
 #include "network.h"
 
 namespace orc {

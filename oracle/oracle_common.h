@@ -10,8 +10,9 @@
 //
 // Parity status: the host-callable subset (march helpers, camera, AABB, triangle, BVH traversal,
 // LD sampler) is pinned bit-exactly against the reference's own headers compiled on the host
-// (oracle/_ref, see oracle/Makefile + tests/test_oracle_vs_ref.py). Device-only bodies (kernels,
-// curand, tcnn grid/MLP) have no reference test or golden vector: "parity unpinned" for those.
+// (oracle/_ref, see oracle/Makefile + tests/test_oracle_pinned.py). Device-only bodies (kernels,
+// curand, tcnn grid/MLP) are pinned against the reference's own device code compiled for sm_100a from the
+// sources where they lie (oracle/Makefile.refdev -> oracle/_ref/libref_dev.so, tests/test_gpu_refdev.py).
 #pragma once
 #include <cmath>
 #include <cstdint>

@@ -408,6 +408,21 @@ class Engine:
         tb._check(tb.lib.snb_reset_accumulation(tb.ctx), "snb_reset_accumulation")     # m_syn_camera_reset -> RayTracer::reset_accumulation (engine.cu:366-369)
         return True
 
+    def skip_frames(self, n=1):
+        """Advance the camera-path position and the animations by `n` frames without rendering or touching the device (frame-batch
+        sharding: a rank walks past the frames other ranks render). The next advance_camera_path / update_world_objects pick up from there."""
+        sc = self.scene
+        if self.is_playing and sc.n_keyframes >= 2:
+            total = self.path_frames or sc.total_frames
+            between = max(1, total // max(sc.n_keyframes - 1, 1))
+            for _ in range(n):
+                self.current_frame += 1
+                if self.current_frame // between + 1 >= sc.n_keyframes:
+                    self.current_frame = 0
+        if self.enable_animations:
+            for _ in range(n):
+                sc.lib.snb_scene_advance(sc.handle)        # host state only; Scene.refresh() runs with the next rendered frame's advance()
+
     def step(self, **kw):
         """One iteration of the reference's main loop, `while (engine.frame())` (src/main.cu:224): camera path, animations, render."""
         self.advance_camera_path()
