@@ -537,7 +537,7 @@ def run_ours(args, rank, local_rank, world):
                 "launch_ms_note": "CUDA events around the march on the context stream (all passes of the batch-schedule iteration; later passes return at once when the first verified); the mesh layer runs concurrently on the second stream",
                 "alone": ({"launch_ms": march_alone_ms, "achieved": algo_bytes / march_alone_ms / 1e6, "frac": algo_bytes / march_alone_ms / 1e6 / hbm,
                            "note": "same kernel, same frames, mesh layer not overlapped (option overlap=0)"} if march_alone_ms else None),
-                "note": "algorithmic bytes = samples x 512 B hash gather + rays x 96 B. With the 2^19 table (24 MB) the gathers are L2 hits by design and DRAM traffic << algorithmic bytes: see the l2 view; with the 2^22 table (c4, 268 MB) they are HBM traffic",
+                "note": "algorithmic bytes = samples x 512 B hash gather + rays x 96 B. With the 2^19 table (24 MB) the gathers are L2 hits by design and DRAM traffic << algorithmic bytes: see the l2 view; with the 2^22 table (c4, 268 MB > L2) ncu still shows 96 % L2 hits (the touched slice fits) and the march time of a frame covers 2-3 passes of the batch-schedule iteration",
                 "tensor": {"achieved_tflops": (samples / K if not cfg.get("batch") else c["samples"]) * FLOP_PER_SAMPLE / max(mm, 1e-9) / 1e9, "peak_tflops": tflops,
                            "note": "both MLPs, padded FLOP, against bf16_tflops_sustained"}}
         if l2:
