@@ -60,7 +60,10 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		if (v == "auto") c->alt_mode = 0;
 		else if (v == "external") c->alt_mode = 1;
 		else if (v == "fixed") c->alt_mode = 2;
-		else return c->fail(SNB_ERR_ARG, "alt_schedule: expected auto | external | fixed");
+		else if (v == "lockstep") c->alt_mode = 3;
+		else return c->fail(SNB_ERR_ARG, "alt_schedule: expected auto | external | fixed | lockstep");
+	} else if (k == "alt_auto_lockstep") {
+		c->alt_auto_lockstep = v != "0";
 	} else if (k == "alt_batch") {
 		const int b = atoi(v.c_str());
 		if (b < 1 || b > 8) return c->fail(SNB_ERR_ARG, "alt_batch: expected 1..8");
@@ -107,7 +110,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
 	// SNB_<OPTION> in the environment sets the default of snb_set_option(ctx, "<option>", ...) (A/B runs without touching the caller)
-	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch", "bvh", "bvh_leaf"};
+	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch", "alt_auto_lockstep", "bvh", "bvh_leaf"};
 	for (const char* opt : kEnvOptions) {
 		std::string env = std::string("SNB_") + opt;
 		for (char& ch : env) ch = (char)toupper((unsigned char)ch);
@@ -115,9 +118,9 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	}
 	if (cuda_stream) c->stream = (cudaStream_t)cuda_stream;
 	else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SNB_ERR_CUDA; } c->own_stream = true; }
-	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(2 * sizeof(NerfCounters)) != cudaSuccess || c->d_alt.reserve(sizeof(AltState)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
+	if (c->d_qctl.reserve(64) != cudaSuccess || c->d_counters.reserve(2 * sizeof(NerfCounters)) != cudaSuccess || c->d_alt.reserve(sizeof(AltState) + sizeof(LockState)) != cudaSuccess) { delete c; return SNB_ERR_CUDA; }
 	cudaMemsetAsync(c->d_counters.p, 0, 2 * sizeof(NerfCounters), c->stream);
-	cudaMemsetAsync(c->d_alt.p, 0, sizeof(AltState), c->stream);
+	cudaMemsetAsync(c->d_alt.p, 0, sizeof(AltState) + sizeof(LockState), c->stream);
 	memset(&c->model, 0, sizeof c->model);
 	*out = c;
 	return SNB_OK;
@@ -129,7 +132,7 @@ void snb_destroy(snb_ctx* c) {
 	cudaStreamSynchronize(c->stream);
 	DevBuf* bufs[] = {&c->d_grid, &c->d_mlp, &c->d_mlp_frag, &c->d_mlp_umma, &c->d_bitfield, &c->d_bits_xyz, &c->d_coarse, &c->d_present, &c->d_objects, &c->d_materials, &c->d_lights, &c->d_queue, &c->d_qctl,
 	                  &c->d_counters, &c->d_alt, &c->d_rng_nerf, &c->d_rng_syn, &c->d_syn_origins, &c->d_syn_dirs, &c->d_syn_rgba, &c->d_syn_depth, &c->d_nerf_fb, &c->d_nerf_depth,
-	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth, &c->d_envmap, &c->d_tris_in, &c->d_bvh_depth, &c->lbvh.keys, &c->lbvh.keys_sorted, &c->lbvh.sort_tmp,
+	                  &c->d_positions, &c->d_normals, &c->d_terms, &c->d_out_rgba, &c->d_out_depth, &c->d_envmap, &c->d_park, &c->d_lock_lists, &c->d_tris_in, &c->d_bvh_depth, &c->lbvh.keys, &c->lbvh.keys_sorted, &c->lbvh.sort_tmp,
 	                  &c->lbvh.islot, &c->lbvh.parent, &c->lbvh.flags, &c->lbvh.bounds};
 	for (DevBuf* b : bufs) b->release();
 	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); o.order.release(); }
@@ -277,6 +280,7 @@ static int upload_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_o
 	c->scene.materials = c->d_materials.as<DevMaterial>(); c->scene.n_materials = n_materials;
 	c->scene.lights = c->d_lights.as<DevLight>(); c->scene.n_lights = n_lights;
 	c->syn_reset = true;   // anything moved -> accumulation restarts (engine.cu:80-127)
+	c->alt_scene_dirty = true;
 	return SNB_OK;
 }
 

@@ -69,14 +69,20 @@ struct snb_ctx {
 	int syn_w = 0, syn_h = 0;
 	snb::DevBuf d_nerf_fb, d_nerf_depth, d_positions, d_normals, d_terms, d_out_rgba, d_out_depth;
 	int fused_blocks_per_sm = 0;
-	int lane_blocks_per_sm[16] = {};   // resident CTAs per SM of each k_nerf_march_fused instance launched by THIS context (0 = not set up yet)
+	int lane_blocks_per_sm[32] = {};   // resident CTAs per SM of each k_nerf_march_fused instance launched by THIS context (0 = not set up yet)
 	int mlp_variant = 0;               // 0 = warp-level mma.sync evaluator, 1 = CTA-level tcgen05/TMEM evaluator (snb_mlp_tc.cuh)
 	int march_variant = 3;             // 3 = one ray per lane + mma.sync MLPs (k_nerf_march_fused: the faster one, default), 6 = warp-specialised tcgen05 pipeline (k_nerf_march_ws)
 	bool ws_ready[8] = {};             // dynamic shared-memory opt-in done for each k_nerf_march_ws instance on this context's device
 	// batch schedule of the sng compositor (AltState in snb_nerf_kernels.cuh): 0 = "auto" (device-resident sequence, verified and
-	// repeated inside the frame), 1 = "external" (one pass; the caller reads the counts and sets the sequence: multi-GPU), 2 = "fixed"
+	// repeated inside the frame; moving frames: lock-step prefix), 1 = "external" (one pass; the caller reads the counts and sets the
+	// sequence: multi-GPU), 2 = "fixed", 3 = "lockstep" (always the lock-step prefix)
 	int alt_mode = 0;
 	int alt_batch = 8;                 // batch length of alt_mode 2
+	bool alt_auto_lockstep = true;     // alt_mode 0: frames whose camera / world moved march the lock-step prefix (option alt_auto_lockstep)
+	bool alt_scene_dirty = true;       // snb_set_scene / snb_update_scene since the last sng NeRF layer
+	float alt_last_cam[12] = {};       // camera and tile size of the last sng NeRF layer
+	int alt_last_tw = 0, alt_last_th = 0;
+	snb::DevBuf d_park, d_lock_lists;  // lock-step prefix: RayPark per queued ray, two lists of queue positions
 	uint32_t alt_target_queries = 2u * 1024u * 1024u;   // target_n_queries of trace_alt (src/testbed_nerf.cu:2188)
 	snb::DevBuf d_alt;
 	// BVH construction (option "bvh"): 0 = the nodes the caller passes (reference builder, parity mode), 1 = linear BVH built on the device

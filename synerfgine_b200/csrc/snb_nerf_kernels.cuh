@@ -51,12 +51,35 @@ struct AltState {                     // device-resident, one per context
 	uint32_t redo;                    // set by k_alt_verify: the pass just made used a sequence its own counts contradict
 	uint32_t passes, converged, last_mismatch;
 };
+// Checkpointed prefix (option alt_schedule=lockstep; chosen by "auto" for frames whose camera or world moved). While the batch length is
+// below 8 the reference's n_alive genuinely couples all rays. Instead of guessing the whole sequence and re-marching the frame when the
+// guess was wrong, the prefix is marched in CHUNKS of kLockChunk batches per launch: every ray parks its compositor state at the end of
+// the chunk, a small kernel checks the chunk's lengths against the counts it produced and either COMMITS the chunk (the parked states
+// become the checkpoint) or corrects the first wrong length and has the next launch redo the chunk FROM THE CHECKPOINT — a wrong guess
+// costs a few batches, not a frame. As soon as a committed length is 8 (n_alive <= target / 8, and it only falls) the rest of the march
+// is one free-running launch from the checkpoint. Per ray the arithmetic is that of the speculative path, so frames are bit-identical.
+constexpr int kLockChunk = 1;
+struct RayPark { float4 rgba; float t, depth, max_weight; uint32_t step_i; };   // 32 B per queued ray, indexed by queue position
+struct LockState {                     // device-resident, behind AltState
+	uint32_t cur_batch;                // checkpoint: batches < cur_batch are committed
+	uint32_t stop_batch;               // the attempt in flight covers [cur_batch, stop_batch)
+	uint32_t done;                     // the committed length of batch cur_batch is 8 (or no ray is left): prefix finished
+	uint32_t sel;                      // which list / park buffer holds the checkpoint
+	uint32_t n_in, n_out;              // rays alive at the checkpoint / parked by the attempt in flight
+	uint32_t attempts, redos;          // statistics
+	unsigned long long pend_samples, pend_hits;   // counters of the attempt in flight (added to NerfCounters on commit)
+};
 struct AltCtl {
 	AltState* st;                     // nullptr: stock path / fixed batch length
 	uint32_t target_queries;          // 2 * 1024 * 1024 in the reference
 	uint32_t fixed_steps;             // != 0: constant batch length (option alt_batch), no counting
 	uint32_t conditional;             // run only if st->redo is set (second and third pass)
 	uint32_t external;                // the caller owns the sequence (a tile of a larger frame): entry 0 is taken from it too
+	// lock-step prefix (PH instances of the lane kernel only)
+	LockState* lk;
+	RayPark* park[2];                 // ping-pong: the checkpoint's states / the states the attempt in flight parks
+	uint32_t* lists[2];               // ping-pong lists of queue positions of the rays still alive
+	uint32_t phase;                   // 0 = not phased, 1 = prefix attempt (one chunk, then park), 2 = final launch (run to completion)
 };
 SNB_HD uint32_t alt_steps_for(uint32_t target, uint32_t n_alive) {
 	uint32_t s = n_alive ? target / n_alive : 8u;
@@ -102,6 +125,58 @@ __global__ void k_alt_verify(AltState* st, uint32_t target, const unsigned int* 
 	st->passes += 1; st->converged = ok ? 1u : 0u; st->last_mismatch = bad;
 	st->redo = (!ok && !last_pass && bad < (uint32_t)kAltSched) ? 1u : 0u;
 }
+// Checkpointed prefix, start of a frame (after ray generation). Batch 0's length is exact (it follows from the ray count); the other
+// entries keep the last frame's values as guesses (8 where there is none). When batch 0 is already 8 there is no prefix.
+__global__ void k_lock_begin(AltState* st, LockState* lk, uint32_t target, const unsigned int* __restrict__ queue_tail, unsigned int* __restrict__ queue_head,
+                             NerfCounters* __restrict__ counters) {
+	const uint32_t j = threadIdx.x;
+	const uint32_t n = *queue_tail;
+	const uint32_t s0 = alt_steps_for(target, n);
+	if (j < (uint32_t)kAltSched) {
+		st->hist[j] = j == 0 ? n : 0u;
+		if (j == 0) st->sched[0] = (uint8_t)s0;
+		else if (st->sched[j] < s0) st->sched[j] = (uint8_t)s0;   // no guess yet (0): assume the length stays; lengths never fall along a march
+	}
+	if (j == 0) {
+		lk->cur_batch = 0; lk->stop_batch = (uint32_t)kLockChunk; lk->sel = 0; lk->n_in = n; lk->n_out = 0; lk->attempts = 0; lk->redos = 0;
+		lk->pend_samples = 0ull; lk->pend_hits = 0ull;
+		lk->done = (s0 >= 8u || n == 0u) ? 1u : 0u;
+		*queue_head = 0u; st->passes = 0; st->redo = 0; st->converged = 0;
+		if (counters) { counters->samples = 0; counters->rays = n; counters->hits = 0; }
+	}
+}
+// After a prefix attempt over [b, stop): hist[j], b < j < stop, are the rays that started batch j in this attempt and n_out the rays
+// parked at `stop`; each is the reference's n_alive_j provided every earlier length of the attempt was right.
+__global__ void k_lock_next(AltState* st, LockState* lk, uint32_t target, unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters) {
+	if (lk->done) return;
+	const uint32_t b = lk->cur_batch, stop = lk->stop_batch;
+	lk->attempts += 1;
+	uint32_t bad = 0xFFFFFFFFu;
+	for (uint32_t j = b + 1; j < stop; ++j) {
+		const uint32_t n = st->hist[j];
+		const uint32_t want = n ? alt_steps_for(target, n) : 8u;
+		if (want != st->sched[j]) { bad = j; st->sched[j] = (uint8_t)want; break; }
+	}
+	if (bad == 0xFFFFFFFFu) {
+		// commit: the parked states are the new checkpoint
+		const uint32_t n = lk->n_out;
+		const uint32_t steps = n ? alt_steps_for(target, n) : 8u;
+		if (stop < (uint32_t)kAltSched) { st->hist[stop] = n; st->sched[stop] = (uint8_t)steps; }
+		for (uint32_t j = stop + 1; j < (uint32_t)kAltSched; ++j) if (st->sched[j] < steps) st->sched[j] = (uint8_t)steps;   // guesses stay monotone
+		lk->cur_batch = stop; lk->sel ^= 1u; lk->n_in = n;
+		lk->stop_batch = stop + (uint32_t)kLockChunk < (uint32_t)kAltSched ? stop + (uint32_t)kLockChunk : (uint32_t)kAltSched;
+		if (counters) { counters->samples += lk->pend_samples; counters->hits += lk->pend_hits; }
+		if (steps >= 8u || n == 0u || stop >= (uint32_t)kAltSched) lk->done = 1u;
+	} else {
+		// redo the chunk from the checkpoint with the corrected length (every entry before `bad` is exact now: progress is guaranteed)
+		for (uint32_t j = bad + 1; j < (uint32_t)kAltSched; ++j) if (st->sched[j] < st->sched[bad]) st->sched[j] = st->sched[bad];
+		for (uint32_t j = b + 1; j < (uint32_t)kAltSched; ++j) st->hist[j] = 0u;
+		lk->redos += 1;
+	}
+	lk->n_out = 0; lk->pend_samples = 0ull; lk->pend_hits = 0ull;
+	*queue_head = 0u;
+}
+
 // Start of a march pass: the first pass always runs and resets the per-frame state; later passes run only after a mismatch and
 // first undo what the previous pass wrote (tile buffers are cleared like ray generation clears them).
 __global__ void __launch_bounds__(256) k_alt_begin_pass(AltState* st, uint32_t first_pass, NerfOut out, uint32_t n_px, unsigned int* __restrict__ queue_head,
@@ -257,7 +332,10 @@ __global__ void __launch_bounds__(128) k_nerf_raygen(DevView view, MarchEnv env,
 
 // Finished ray -> pixel (extract_from_payload for the sng path, shade_kernel_nerf for the stock path). Runs once per
 // ray, so it is kept out of line: the march loop has to stay small (instruction cache).
-__device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out, bool alt, int render_mode, uint32_t idx, v3 dir, float t, float4 rgba, float depth) {
+// `rewrite`: the pixel may hold the result of an abandoned prefix attempt (checkpointed prefix): every field is written, those a clean
+// frame would leave untouched get the values ray generation cleared them to.
+__device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out, bool alt, int render_mode, uint32_t idx, v3 dir, float t, float4 rgba, float depth,
+                                         bool rewrite = false) {
 	const int l = tile_local_index(view, idx);
 	float4 tmp = rgba;
 	if (alt) {
@@ -275,6 +353,13 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 		out.fb[l] = make_float4(tmp.x + bg.x * k, tmp.y + bg.y * k, tmp.z + bg.z * k, tmp.w + bg.w * k);
 	} else out.fb[l] = tmp;   // frame buffer was cleared to 0 by ray generation: tmp + 0 * (1 - a)
 	if (tmp.w > 0.2f) out.depth[l] = depth;
+	else if (rewrite) out.depth[l] = kMaxDepth;
+}
+__device__ __noinline__ void clear_pixel(const DevView& view, const NerfOut& out, uint32_t idx) {
+	const int l = tile_local_index(view, idx);
+	out.fb[l] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+	out.depth[l] = kMaxDepth;
+	if (out.positions) { out.positions[l * 3 + 0] = 0.0f; out.positions[l * 3 + 1] = 0.0f; out.positions[l * 3 + 2] = 0.0f; }
 }
 
 // ---- the persistent fused kernel -----------------------------------------------------------------------------------
@@ -303,11 +388,13 @@ constexpr int kMinFill = SNB_LANE_MIN_FILL;
 constexpr int kFusedWarpsFew = 10;
 constexpr int lane_smem_bytes(int w) { return kFragWords * 4 + w * kWarpSmemBytes + (int)sizeof(LevelDesc) * kMaxLevels + kCoarseWords * 4; }
 constexpr int kLaneSmemBytes = lane_smem_bytes(kFusedWarps);
-template <int F, bool ALT, int W>
+// PH = lock-step prefix instance (see LockState): rays resume from / park into RayPark records at batch boundaries.
+template <int F, bool ALT, int W, bool PH = false>
 __global__ void __launch_bounds__(W * 32, SNB_LANE_CTAS)
 k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, const RayRec* __restrict__ queue, const unsigned int* __restrict__ queue_tail,
                    unsigned int* __restrict__ queue_head, NerfCounters* __restrict__ counters, AltCtl alt) {
 	if (alt.conditional && !alt.st->redo) return;   // second / third pass of the batch-schedule iteration: only after a mismatch (uniform)
+	if (PH && alt.phase == 1 && alt.lk->done) return;   // prefix launch enqueued for a batch the frame did not need (uniform)
 	// dynamic shared memory (kLaneSmemBytes): [fragment-ordered weights | per-warp staging + output tiles | level table | look-ahead grid]
 	extern __shared__ __align__(16) unsigned char s_lane[];
 	uint32_t* s_w = reinterpret_cast<uint32_t*>(s_lane);
@@ -321,10 +408,19 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	// batch schedule of the sng compositor (see AltState): lengths of batches 0..kAltSched-1 (8 afterwards) and this CTA's share of the counts
 	__shared__ uint8_t s_sched[kAltSched];
 	__shared__ uint32_t s_hist[kAltSched];
-	const unsigned int n_rays = *queue_tail;
+	const unsigned int n_rays = PH ? alt.lk->n_in : *queue_tail;
+	const uint32_t batch0 = PH ? alt.lk->cur_batch : 0u;                     // PH: the batch every ray of this launch starts with
+	const bool resume = PH && batch0 > 0u;
+	const uint32_t stop_batch = (PH && alt.phase == 1) ? alt.lk->stop_batch : 0xFFFFFFFFu;
+	const uint32_t sel = PH ? alt.lk->sel : 0u;
+	const uint32_t* __restrict__ list_in = PH ? alt.lists[sel] : nullptr;
+	uint32_t* __restrict__ list_out = PH ? alt.lists[sel ^ 1u] : nullptr;
+	const RayPark* __restrict__ park_in = PH ? alt.park[sel] : nullptr;
+	RayPark* __restrict__ park_out = PH ? alt.park[sel ^ 1u] : nullptr;
 	if (threadIdx.x < kAltSched) {
 		uint32_t steps = kBatchSteps;
 		if (ALT && alt.fixed_steps) steps = alt.fixed_steps;
+		else if (PH) steps = alt.st->sched[threadIdx.x];                      // exact up to batch0, guesses beyond (k_lock_begin / k_lock_next)
 		else if (ALT && alt.st) {
 			const uint32_t s0 = alt_steps_for(alt.target_queries, n_rays);
 			steps = (threadIdx.x == 0 && !alt.external) ? s0 : alt.st->sched[threadIdx.x];
@@ -349,6 +445,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 	float t = 0.0f, depth = 0.0f;
 	float4 rgba = make_float4(0, 0, 0, 0);
 	uint32_t idx = 0, step_i = 1;
+	uint32_t qpos = 0;   // PH: queue position of the slot's ray (its RayPark record)
 	int k = 0, n_empty = 0;
 	uint32_t batch = 0, batch_steps = s_sched[0];   // index and length of the ray's current batch
 	bool alive = false, drained = false;
@@ -364,7 +461,8 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		alive = false;
 		if (step_i + batch_steps >= kMarchIter) return;   // died in the last possible iteration: never compacted into the hit list
 		if (ALT) t = depth / dot(cam_fwd, d);             // payload.t rewrite at the end of composite_kernel_nerf_alt
-		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth); ++n_hits; }
+		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth, PH); ++n_hits; }
+		else if (PH) clear_pixel(view, out, idx);   // an abandoned attempt may have written this pixel: back to the cleared state
 	};
 
 	bool fin = false;   // ray ended in the previous iteration: one finish() site keeps the loop small
@@ -378,16 +476,26 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			base = __shfl_sync(0xFFFFFFFFu, base, 0);
 			const unsigned int mine = base + __popc(need & ((1u << lane) - 1u));
 			if (!alive && mine < n_rays) {
-				const float4 q0 = __ldg(reinterpret_cast<const float4*>(queue + mine));
-				const float4 q1 = __ldg(reinterpret_cast<const float4*>(queue + mine) + 1);
+				const unsigned int qp = resume ? list_in[mine] : mine;
+				const float4 q0 = __ldg(reinterpret_cast<const float4*>(queue + qp));
+				const float4 q1 = __ldg(reinterpret_cast<const float4*>(queue + qp) + 1);
 				o = mk3(q0.x, q0.y, q0.z); t = q0.w; d = mk3(q1.x, q1.y, q1.z); idx = __float_as_uint(q1.w);
 				idir = 1.0f / d;
 				rgba = make_float4(0, 0, 0, 0); depth = 0.0f; max_weight = 0.0f; step_i = 1; k = 0; n_empty = 0; alive = true;
 				batch = 0; batch_steps = s_sched[0];
-				if (count_batches) atomicAdd(&s_hist[0], 1u);
-				++n_launched;
+				if (PH) {
+					qpos = qp;
+					if (resume) {   // compositor state as it was at the end of batch batch0 - 1
+						const RayPark pk = park_in[qp];
+						rgba = pk.rgba; t = pk.t; depth = pk.depth; max_weight = pk.max_weight; step_i = pk.step_i;
+						batch = batch0; batch_steps = batch0 < (uint32_t)kAltSched ? s_sched[batch0] : (uint32_t)kBatchSteps;
+					}
+				} else {
+					if (count_batches) atomicAdd(&s_hist[0], 1u);
+					++n_launched;
+				}
 				// SH block of the staged row (k-tile 2): encoded by ray generation, copied as is
-				const uint4 s0 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 2), s1 = __ldg(reinterpret_cast<const uint4*>(queue + mine) + 3);
+				const uint4 s0 = __ldg(reinterpret_cast<const uint4*>(queue + qp) + 2), s1 = __ldg(reinterpret_cast<const uint4*>(queue + qp) + 3);
 				uint4* dst = reinterpret_cast<uint4*>(tile + lane * kTileStrideH + kTileShCol);
 				dst[0] = s0; dst[1] = s1;
 			}
@@ -475,7 +583,14 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 				if (step_i >= kMarchIter) alive = false;         // iteration budget exhausted: ray is dropped, not written
 				else {
 					++batch;
-					if (batch < (uint32_t)kAltSched) { batch_steps = s_sched[batch]; if (count_batches) atomicAdd(&s_hist[batch], 1u); }
+					if (PH && batch == stop_batch) {
+						// lock-step prefix: park at the batch boundary; the number of parked rays is n_alive of the next batch
+						RayPark pk; pk.rgba = rgba; pk.t = t; pk.depth = depth; pk.max_weight = max_weight; pk.step_i = step_i;
+						park_out[qpos] = pk;
+						list_out[atomicAdd(&alt.lk->n_out, 1u)] = qpos;
+						alive = false;
+					}
+					else if (batch < (uint32_t)kAltSched) { batch_steps = s_sched[batch]; if (count_batches) atomicAdd(&s_hist[batch], 1u); }
 					else batch_steps = ALT && alt.fixed_steps ? alt.fixed_steps : kBatchSteps;
 				}
 			}
@@ -489,7 +604,9 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		n_hits += __shfl_xor_sync(0xFFFFFFFFu, n_hits, s);
 		n_launched += __shfl_xor_sync(0xFFFFFFFFu, n_launched, s);
 	}
-	if (lane == 0 && counters) {
+	if (PH && alt.phase == 1) {   // a prefix attempt: its counts become final only when k_lock_next commits the chunk
+		if (lane == 0) { atomicAdd(&alt.lk->pend_samples, (unsigned long long)n_samples); atomicAdd(&alt.lk->pend_hits, (unsigned long long)n_hits); }
+	} else if (lane == 0 && counters) {
 		atomicAdd(&counters->samples, (unsigned long long)n_samples);
 		atomicAdd(&counters->hits, (unsigned long long)n_hits);
 		atomicAdd(&counters->rays, (unsigned long long)n_launched);

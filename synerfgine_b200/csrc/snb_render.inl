@@ -34,18 +34,18 @@ static int check_view(snb_ctx* c, const snb_view* v, const snb_tile* t) {
 
 // Per-context, per-kernel-variant launch set-up (the dynamic shared-memory opt-in is a per-device attribute and a context belongs to
 // one device; nothing process-wide is cached).
-template <int F, bool ALT, int W>
+template <int F, bool ALT, int W, bool PH = false>
 static int launch_lane(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
-	const int slot = (F == 1 ? 0 : F == 2 ? 1 : F == 4 ? 2 : 3) * 4 + (ALT ? 2 : 0) + (W == kFusedWarps ? 1 : 0);
+	const int slot = (F == 1 ? 0 : F == 2 ? 1 : F == 4 ? 2 : 3) * 4 + (ALT ? 2 : 0) + (W == kFusedWarps ? 1 : 0) + (PH ? 16 : 0);
 	int& per_sm = c->lane_blocks_per_sm[slot];
 	if (per_sm == 0) {
-		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, lane_smem_bytes(W)));
-		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT, W>, W * 32, lane_smem_bytes(W)));
+		SNB_CUDA(c, cudaFuncSetAttribute(k_nerf_march_fused<F, ALT, W, PH>, cudaFuncAttributeMaxDynamicSharedMemorySize, lane_smem_bytes(W)));
+		SNB_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nerf_march_fused<F, ALT, W, PH>, W * 32, lane_smem_bytes(W)));
 		per_sm = std::max(1, per_sm);
 	}
 	c->fused_blocks_per_sm = per_sm;
 	const int blocks = std::max(1, std::min(c->sm_count * per_sm, (n_px + W * 32 - 1) / (W * 32)));
-	k_nerf_march_fused<F, ALT, W><<<blocks, W * 32, lane_smem_bytes(W), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt);
+	k_nerf_march_fused<F, ALT, W, PH><<<blocks, W * 32, lane_smem_bytes(W), c->stream>>>(c->model, dv, out, render_mode, queue, qctl, qctl + 1, c->d_counters.as<NerfCounters>(), alt);
 	SNB_LAUNCHED(c);
 	return SNB_OK;
 }
@@ -70,9 +70,13 @@ template <int F, bool ALT>
 static int launch_fused(snb_ctx* c, const DevView& dv, const NerfOut& out, int render_mode, int n_px, const RayRec* queue, unsigned int* qctl, const AltCtl& alt) {
 	// "ws": warp-specialised tcgen05 pipeline (default). The stock path's Positions / Depth visualisations need the sample position in
 	// the compositor, which only the lane kernel carries.
-	if (c->march_variant == 6 && (ALT || (render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH))) return launch_ws<F, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
+	if (c->march_variant == 6 && !alt.phase && (ALT || (render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH))) return launch_ws<F, ALT>(c, dv, out, render_mode, n_px, queue, qctl, alt);
 	// CTA shape by the rays a lane will see (option "lane_warps": 0 = by tile size, else 10 | 12): results do not depend on it
 	const bool few = c->lane_warps ? c->lane_warps == kFusedWarpsFew : (size_t)n_px < (size_t)c->sm_count * SNB_LANE_CTAS * kFusedWarps * 32 * 16;
+	if constexpr (ALT) {
+		if (alt.phase)   // lock-step prefix instance (lane kernel only)
+			return few ? launch_lane<F, true, kFusedWarpsFew, true>(c, dv, out, render_mode, n_px, queue, qctl, alt) : launch_lane<F, true, kFusedWarps, true>(c, dv, out, render_mode, n_px, queue, qctl, alt);
+	}
 	return few ? launch_lane<F, ALT, kFusedWarpsFew>(c, dv, out, render_mode, n_px, queue, qctl, alt) : launch_lane<F, ALT, kFusedWarps>(c, dv, out, render_mode, n_px, queue, qctl, alt);
 }
 
@@ -92,6 +96,7 @@ static int launch_fused_f(snb_ctx* c, const DevView& dv, const NerfOut& out, int
 // frame to frame; a pass whose own ray counts contradict the lengths it used is repeated (at most kAltPasses passes, each later
 // one a conditional launch that returns at once when the previous pass verified) — all enqueued without a host round trip.
 static const int kAltPasses = 4;
+static const int kLockAttempts = 16;  // prefix chunk attempts enqueued per moving frame (kLockChunk batches each; C2 needs 1)
 static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render_mode, float* fb, float* depth, float* positions) {
 	if (!c->has_model) return c->fail(SNB_ERR_STATE, "no model: call snb_set_model first");
 	const int n_px = dv.tw * dv.th;
@@ -111,6 +116,7 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	c->stage_begin(1);
 	int rc = SNB_OK;
 	AltCtl ctl; ctl.st = nullptr; ctl.target_queries = c->alt_target_queries; ctl.fixed_steps = 0; ctl.conditional = 0; ctl.external = c->alt_mode == 1;
+	ctl.lk = nullptr; ctl.park[0] = ctl.park[1] = nullptr; ctl.lists[0] = ctl.lists[1] = nullptr; ctl.phase = 0;
 	if (!alt) {
 		// Testbed::render_nerf hands camera_matrix1 to the compositor (src/testbed_nerf.cu:2761): depth is measured along the END-of-shutter camera
 		DevView mv = dv;
@@ -122,7 +128,38 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 		AltState* st = c->d_alt.as<AltState>();
 		ctl.st = st;
 		const int passes = c->alt_mode == 1 ? 1 : kAltPasses;   // "external": the caller owns the sequence (multi-GPU: counts are summed over ranks)
-		for (int pass = 0; pass < passes && rc == SNB_OK; ++pass) {
+		// "auto": a frame whose camera or world moved since the last one would need its batch lengths guessed (and re-marched when the guess
+		// is wrong): it marches the lock-step prefix instead. A still frame keeps the verified sequence of the last one: one speculative pass.
+		const bool moved = c->alt_scene_dirty || std::memcmp(&dv.cam, c->alt_last_cam, sizeof c->alt_last_cam) != 0 || dv.tw != c->alt_last_tw || dv.th != c->alt_last_th;
+		std::memcpy(c->alt_last_cam, &dv.cam, sizeof c->alt_last_cam); c->alt_last_tw = dv.tw; c->alt_last_th = dv.th; c->alt_scene_dirty = false;
+		const bool lockstep = c->march_variant == 3 && (c->alt_mode == 3 || (c->alt_mode == 0 && c->alt_auto_lockstep && moved));
+		int first_pass = 0;
+		if (lockstep) {
+			LockState* lk = reinterpret_cast<LockState*>(st + 1);
+			const size_t cap = (size_t)patches * 32 + 64;
+			SNB_CUDA(c, c->d_park.reserve(cap * 2 * sizeof(RayPark)));
+			SNB_CUDA(c, c->d_lock_lists.reserve(cap * 2 * sizeof(uint32_t)));
+			ctl.lk = lk; ctl.park[0] = c->d_park.as<RayPark>(); ctl.park[1] = ctl.park[0] + cap;
+			ctl.lists[0] = c->d_lock_lists.as<uint32_t>(); ctl.lists[1] = ctl.lists[0] + cap;
+			k_lock_begin<<<1, kAltSched, 0, c->stream>>>(st, lk, c->alt_target_queries, qctl, qctl + 1, c->d_counters.as<NerfCounters>());
+			SNB_LAUNCHED(c);
+			ctl.phase = 1;
+			for (int p = 0; p < kLockAttempts && rc == SNB_OK; ++p) {   // chunk attempts; those beyond the frame's prefix return at once (lk->done)
+				rc = launch_fused_f<true>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl);
+				if (rc != SNB_OK) break;
+				k_lock_next<<<1, 1, 0, c->stream>>>(st, lk, c->alt_target_queries, qctl + 1, c->d_counters.as<NerfCounters>());
+				SNB_LAUNCHED(c);
+			}
+			ctl.phase = 2;
+			if (rc == SNB_OK) rc = launch_fused_f<true>(c, dv, out, render_mode, patches * 32, q0, qctl, ctl);
+			if (rc == SNB_OK) {
+				k_alt_verify<<<1, kAltSched, 0, c->stream>>>(st, c->alt_target_queries, qctl, 0u, 0u);   // exact unless the prefix outlasted the attempts: then the passes below repair it
+				SNB_LAUNCHED(c);
+			}
+			ctl.phase = 0; ctl.lk = nullptr;
+			first_pass = 1;
+		}
+		for (int pass = first_pass; pass < passes && rc == SNB_OK; ++pass) {
 			k_alt_begin_pass<<<pass == 0 ? 1 : std::min(2 * c->sm_count, (n_px + 255) / 256), 256, 0, c->stream>>>(st, pass == 0, out, (uint32_t)n_px, qctl + 1, c->d_counters.as<NerfCounters>());
 			SNB_LAUNCHED(c);
 			ctl.conditional = pass > 0;

@@ -419,3 +419,75 @@ def test_set_model_from_device_memory_renders_identically(snb):
             snb.snb_destroy(c)
     assert frames[0][0][..., 3].max() > 0.5
     assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+
+
+@pytest.mark.parametrize("kind,w,h,target", [("small16x2", 128, 96, 17500), ("fox8x4", 64, 64, 7606), ("small16x2", 96, 64, 2097152)])
+def test_lockstep_prefix_equals_the_speculative_schedule(snb, orc, ctx, kind, w, h, target):
+    """alt_schedule=lockstep (what "auto" uses for frames whose camera or world moved): the batches shorter than 8 are marched one per
+    launch (up to 16) with the rays parked in between, so the sequence is exact in ONE pass whatever the previous frame was. Every ray does the same
+    arithmetic as under the speculative schedule once that has converged: frames, positions, counts and sequence are bit-identical —
+    for a cold start and along a moving camera."""
+    m = common.model(kind)
+    set_model(snb, ctx, m)
+    assert snb.snb_set_option(ctx, b"march", b"lane") == 0
+    assert snb.snb_set_option(ctx, b"alt_target_queries", str(target).encode()) == 0
+    rt = common.default_rt(show_shadow_on_nerf=0)
+    cams = [common.camera_matrix(), common.camera_matrix(view=(-0.22, -0.47, -0.86), at=(0.55, 0.43, 0.5)), common.camera_matrix(view=(0.3, -0.4, -0.8), zoom=0.8),
+            common.camera_matrix(view=(0.3, -0.4, -0.8), zoom=0.8)]
+    bufs = lambda: (dev((h, w, 4), torch.float32), dev((h, w), torch.float32), dev((h, w, 3), torch.float32), dev((h, w, 3), torch.float32))
+
+    def render(v, b):
+        rc = snb.snb_render_nerf_with_buffers(ctx, C.byref(v), None, C.byref(rt), 1, b[0].data_ptr(), b[1].data_ptr(), b[2].data_ptr(), b[3].data_ptr())
+        assert rc == 0, snb.snb_last_error(ctx)
+        return _alt_status(snb, ctx)
+    try:
+        # reference frames: speculation only, repeated until converged
+        assert snb.snb_set_option(ctx, b"alt_schedule", b"auto") == 0 and snb.snb_set_option(ctx, b"alt_auto_lockstep", b"0") == 0
+        want = []
+        for cam in cams:
+            v = common.make_view(w, h, cam=cam)
+            b = bufs()
+            for _ in range(6):
+                st = render(v, b)
+                if st["converged"]:
+                    break
+            assert st["converged"] == 1
+            want.append(([x.cpu().numpy() for x in b[:3]], st))
+        multi = sum(1 for _, st in want if st["passes"] > 1)
+        # lock step, cold start, then along the same camera sequence: one pass each, identical results
+        assert snb.snb_set_alt_schedule(ctx, None, 0) == 0
+        assert snb.snb_set_option(ctx, b"alt_schedule", b"lockstep") == 0
+        for cam, (ref, rst) in zip(cams, want):
+            v = common.make_view(w, h, cam=cam)
+            b = bufs()
+            st = render(v, b)
+            prefix = int((rst["sched"] < 8).sum())
+            if prefix <= 16:                      # kLockAttempts: a longer prefix falls back to verified speculation (more passes, same frame)
+                assert st["passes"] == 1 and st["converged"] == 1, st
+            for _ in range(6):
+                if st["converged"]:
+                    break
+                st = render(v, b)
+            assert st["converged"] == 1, st
+            k = 24
+            np.testing.assert_array_equal(st["sched"][:k], rst["sched"][:k]); np.testing.assert_array_equal(st["alive"][:k], rst["alive"][:k])
+            for got, exp in zip(b[:3], ref):
+                assert np.array_equal(got.cpu().numpy(), exp)
+        if target < 2097152:
+            assert min(want[0][1]["sched"][:4]) < 8, "degenerate test: no prefix"
+        # "auto" picks the lock-step prefix when the camera moved and plain speculation when it did not
+        assert snb.snb_set_option(ctx, b"alt_schedule", b"auto") == 0 and snb.snb_set_option(ctx, b"alt_auto_lockstep", b"1") == 0
+        for cam, (ref, rst) in zip(cams, want):
+            b = bufs()
+            v = common.make_view(w, h, cam=cam)
+            st = render(v, b)
+            for _ in range(6):
+                if st["converged"]:
+                    break
+                st = render(v, b)
+            assert st["converged"] == 1 and (st["passes"] == 1 or int((rst["sched"] < 8).sum()) > 16), st
+            assert np.array_equal(b[0].cpu().numpy(), ref[0])
+        print(f"[lockstep {kind} {w}x{h}] frames that needed several speculative passes: {multi} of {len(cams)}")
+    finally:
+        snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_auto_lockstep", b"1"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152")
+        snb.snb_set_alt_schedule(ctx, None, 0)
