@@ -163,7 +163,10 @@ const char* snb_last_error(const snb_ctx* ctx);
 int snb_sync(snb_ctx* ctx);
 const char* snb_version(void);
 /* Options. Semantics (these change what is computed; the defaults are the reference's behaviour):
- *   "alt_schedule" = "auto" (default) | "external" | "fixed"   batch lengths of the sng compositor, see snb_get_alt_status below
+ *   "alt_schedule" = "auto" (default) | "external" | "fixed" | "lockstep"   batch lengths of the sng compositor, see snb_get_alt_status below
+ *                    (auto: a still frame re-uses the verified sequence of the last one; a frame whose camera or tile changed marches
+ *                    the batches shorter than 8 in lock step, one per launch, from parked ray states: exact in one pass. lockstep: always.
+ *                    "alt_auto_lockstep" = "0" keeps auto on verified speculation only)
  *   "alt_batch"    = "1".."8"        batch length of alt_schedule = fixed
  *   "alt_target_queries" = "2097152" target_n_queries of NerfTracer::trace_alt (src/testbed_nerf.cu:2188); tests lower it to exercise short batches on small frames
  * Implementation selectors (A/B measurements; frames are bit-identical unless noted):
@@ -238,6 +241,12 @@ int snb_accumulate_tonemap(snb_ctx* ctx, int n_pixels, const float* frame_rgba_d
 int snb_frame(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_dev, float* out_depth_dev);
 /* … or copied into host buffers (tile-sized; what a host-language caller over cgo/JNI/ctypes uses). */
 int snb_frame_host(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_host, float* out_depth_host);
+/* The same for callers that stream frames (the reference's main loop presents frame after frame): returns once the frame and its
+ * device-to-host copy are enqueued; the copy runs on its own stream while the next frame renders. slot = 0 | 1 names the double buffer
+ * (device and host side); read a slot's host buffers after snb_frame_host_wait(ctx, slot), reuse them only after it. The host buffers
+ * should be pinned, else the copy is staged synchronously. */
+int snb_frame_host_async(snb_ctx* ctx, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_host, float* out_depth_host, int32_t slot);
+int snb_frame_host_wait(snb_ctx* ctx, int32_t slot);
 
 /* ---- parity taps (the reference's debug views: positions, depth, hit indices — SURVEY.md §4) -------------- */
 /* Per-ray march sample sequence: t, dt, cell = mip << 24 | morton (0xFFFFFFFF padding), n per ray. */

@@ -90,6 +90,8 @@ SIGNATURES = {
     "snb_accumulate_tonemap": (C.c_int, [vp, C.c_int, vp, vp, u32, C.c_int, C.c_int, f32, pf32, C.c_int, vp]),
     "snb_frame": (C.c_int, [vp, C.POINTER(View), C.POINTER(Tile), C.POINTER(RtParams), vp, vp]),
     "snb_frame_host": (C.c_int, [vp, C.POINTER(View), C.POINTER(Tile), C.POINTER(RtParams), vp, vp]),
+    "snb_frame_host_async": (C.c_int, [vp, C.POINTER(View), C.POINTER(Tile), C.POINTER(RtParams), vp, vp, i32]),
+    "snb_frame_host_wait": (C.c_int, [vp, i32]),
     "snb_march_trace": (C.c_int, [vp, C.POINTER(View), u32, vp, vp, vp, vp, vp]),
     "snb_network_inference": (C.c_int, [vp, vp, u64, vp, vp, vp]),
     "snb_trace_rays": (C.c_int, [vp, vp, u32, vp, vp, vp]),

@@ -136,6 +136,10 @@ void snb_destroy(snb_ctx* c) {
 	                  &c->lbvh.islot, &c->lbvh.parent, &c->lbvh.flags, &c->lbvh.bounds};
 	for (DevBuf* b : bufs) b->release();
 	for (auto& o : c->obj_store) { o.nodes.release(); o.tris.release(); o.order.release(); }
+	if (c->copy_stream) {
+		cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream);
+		for (int k = 0; k < 2; ++k) { cudaEventDestroy(c->ev_frame_done[k]); cudaEventDestroy(c->ev_copy_done[k]); c->d_pipe_rgba[k].release(); c->d_pipe_depth[k].release(); }
+	}
 	if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
@@ -280,7 +284,6 @@ static int upload_scene_pods(snb_ctx* c, const snb_object* objects, uint32_t n_o
 	c->scene.materials = c->d_materials.as<DevMaterial>(); c->scene.n_materials = n_materials;
 	c->scene.lights = c->d_lights.as<DevLight>(); c->scene.n_lights = n_lights;
 	c->syn_reset = true;   // anything moved -> accumulation restarts (engine.cu:80-127)
-	c->alt_scene_dirty = true;
 	return SNB_OK;
 }
 

@@ -78,10 +78,10 @@ struct snb_ctx {
 	// sequence: multi-GPU), 2 = "fixed", 3 = "lockstep" (always the lock-step prefix)
 	int alt_mode = 0;
 	int alt_batch = 8;                 // batch length of alt_mode 2
-	bool alt_auto_lockstep = true;     // alt_mode 0: frames whose camera / world moved march the lock-step prefix (option alt_auto_lockstep)
-	bool alt_scene_dirty = true;       // snb_set_scene / snb_update_scene since the last sng NeRF layer
+	bool alt_auto_lockstep = true;     // alt_mode 0: frames whose camera or tile changed march the lock-step prefix (option alt_auto_lockstep); the march never reads the scene
 	float alt_last_cam[12] = {};       // camera and tile size of the last sng NeRF layer
-	int alt_last_tw = 0, alt_last_th = 0;
+	int alt_last_tw = 0, alt_last_th = 0, alt_last_tx0 = 0, alt_last_ty0 = 0;
+	float alt_last_focal = 0.0f;
 	snb::DevBuf d_park, d_lock_lists;  // lock-step prefix: RayPark per queued ray, two lists of queue positions
 	uint32_t alt_target_queries = 2u * 1024u * 1024u;   // target_n_queries of trace_alt (src/testbed_nerf.cu:2188)
 	snb::DevBuf d_alt;
@@ -107,6 +107,11 @@ struct snb_ctx {
 	// latency-bound, so they run concurrently (the reference serialises them with host syncs, engine.cu:386-406)
 	cudaStream_t stream2 = nullptr;   // mesh layer
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	// snb_frame_host_async: copy stream + double-buffered device outputs
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t ev_frame_done[2] = {}, ev_copy_done[2] = {};
+	snb::DevBuf d_pipe_rgba[2], d_pipe_depth[2];
+	bool pipe_used[2] = {false, false};
 	bool overlap_layers = true;
 	int mesh_priority = 1;         // stream priority of the mesh layer's stream: +1 high (default: the mesh layer finishes under ray generation and the march runs undisturbed), 0 default, -1 low (option "mesh_priority")
 	int lane_warps = 0;            // lane march CTA shape: 0 = chosen by tile size, 10 | 12 = forced (option "lane_warps")

@@ -128,10 +128,12 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 		AltState* st = c->d_alt.as<AltState>();
 		ctl.st = st;
 		const int passes = c->alt_mode == 1 ? 1 : kAltPasses;   // "external": the caller owns the sequence (multi-GPU: counts are summed over ranks)
-		// "auto": a frame whose camera or world moved since the last one would need its batch lengths guessed (and re-marched when the guess
-		// is wrong): it marches the lock-step prefix instead. A still frame keeps the verified sequence of the last one: one speculative pass.
-		const bool moved = c->alt_scene_dirty || std::memcmp(&dv.cam, c->alt_last_cam, sizeof c->alt_last_cam) != 0 || dv.tw != c->alt_last_tw || dv.th != c->alt_last_th;
-		std::memcpy(c->alt_last_cam, &dv.cam, sizeof c->alt_last_cam); c->alt_last_tw = dv.tw; c->alt_last_th = dv.th; c->alt_scene_dirty = false;
+		// "auto": a frame whose camera (or tile) changed since the last one would need its batch lengths guessed (and re-marched when the
+		// guess is wrong): it marches the lock-step prefix instead. A still frame keeps the verified sequence of the last one: one speculative
+		// pass. The march reads the model and the view only — moving OBJECTS do not change n_alive — so the scene does not enter the test.
+		const bool moved = std::memcmp(&dv.cam, c->alt_last_cam, sizeof c->alt_last_cam) != 0 || dv.tw != c->alt_last_tw || dv.th != c->alt_last_th || dv.tx0 != c->alt_last_tx0 || dv.ty0 != c->alt_last_ty0 ||
+		                   dv.focal.x != c->alt_last_focal;
+		std::memcpy(c->alt_last_cam, &dv.cam, sizeof c->alt_last_cam); c->alt_last_tw = dv.tw; c->alt_last_th = dv.th; c->alt_last_tx0 = dv.tx0; c->alt_last_ty0 = dv.ty0; c->alt_last_focal = dv.focal.x;
 		const bool lockstep = c->march_variant == 3 && (c->alt_mode == 3 || (c->alt_mode == 0 && c->alt_auto_lockstep && moved));
 		int first_pass = 0;
 		if (lockstep) {
@@ -384,6 +386,43 @@ int snb_frame_host(snb_ctx* c, const snb_view* view, const snb_tile* tile, const
 	SNB_CUDA(c, cudaMemcpyAsync(out_rgba_host, c->d_out_rgba.p, n * 16, cudaMemcpyDeviceToHost, c->stream));
 	if (out_depth_host) SNB_CUDA(c, cudaMemcpyAsync(out_depth_host, c->d_out_depth.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
 	SNB_CUDA(c, cudaStreamSynchronize(c->stream));
+	return SNB_OK;
+}
+
+// Pipelined form of snb_frame_host for callers that stream frames: the device-to-host copy of frame i runs on a copy stream while
+// frame i + 1 renders. `slot` (0 | 1) names the double buffer; a slot's host buffers (pinned memory, or the copy is not asynchronous)
+// may be read after snb_frame_host_wait(ctx, slot) and must not be reused before it.
+int snb_frame_host_async(snb_ctx* c, const snb_view* view, const snb_tile* tile, const snb_rt_params* rt, float* out_rgba_host, float* out_depth_host, int32_t slot) {
+	if (!c || !out_rgba_host || slot < 0 || slot > 1) return SNB_ERR_ARG;
+	int rc = check_view(c, view, tile); if (rc) return rc;
+	const DevView dv = make_view(view, tile);
+	const size_t n = (size_t)dv.tw * dv.th;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	if (!c->copy_stream) {
+		SNB_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+		for (int k = 0; k < 2; ++k) { SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_frame_done[k], cudaEventDisableTiming)); SNB_CUDA(c, cudaEventCreateWithFlags(&c->ev_copy_done[k], cudaEventDisableTiming)); }
+	}
+	if (c->d_pipe_rgba[slot].cap < n * 16 || c->d_pipe_depth[slot].cap < n * 4) {
+		SNB_CUDA(c, cudaStreamSynchronize(c->copy_stream));       // growing a buffer a copy may still read
+		SNB_CUDA(c, c->d_pipe_rgba[slot].reserve(n * 16));
+		SNB_CUDA(c, c->d_pipe_depth[slot].reserve(n * 4));
+	}
+	if (c->pipe_used[slot]) SNB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copy_done[slot], 0));   // the slot's last copy has left the device buffer
+	rc = snb_frame(c, view, tile, rt, c->d_pipe_rgba[slot].as<float>(), c->d_pipe_depth[slot].as<float>()); if (rc) return rc;
+	SNB_CUDA(c, cudaEventRecord(c->ev_frame_done[slot], c->stream));
+	SNB_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_frame_done[slot], 0));
+	SNB_CUDA(c, cudaMemcpyAsync(out_rgba_host, c->d_pipe_rgba[slot].p, n * 16, cudaMemcpyDeviceToHost, c->copy_stream));
+	if (out_depth_host) SNB_CUDA(c, cudaMemcpyAsync(out_depth_host, c->d_pipe_depth[slot].p, n * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+	SNB_CUDA(c, cudaEventRecord(c->ev_copy_done[slot], c->copy_stream));
+	c->pipe_used[slot] = true;
+	return SNB_OK;
+}
+
+int snb_frame_host_wait(snb_ctx* c, int32_t slot) {
+	if (!c || slot < 0 || slot > 1) return SNB_ERR_ARG;
+	if (!c->pipe_used[slot]) return SNB_OK;
+	SNB_CUDA(c, cudaSetDevice(c->device));
+	SNB_CUDA(c, cudaEventSynchronize(c->ev_copy_done[slot]));
 	return SNB_OK;
 }
 

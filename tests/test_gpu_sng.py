@@ -400,3 +400,46 @@ def test_headless_cli_renders_an_animated_path_to_png(tmp_path):
     blobs = [open(out % i, "rb").read() for i in range(3)]
     assert all(b[:8] == b"\x89PNG\r\n\x1a\n" and len(b) > 1000 for b in blobs)
     assert blobs[0] != blobs[1] and blobs[1] != blobs[2]
+
+
+def test_streamed_host_frames_equal_the_synchronous_ones(snb, ctx):
+    """snb_frame_host_async / snb_frame_host_wait: the device-to-host copy of a frame overlaps the next frame's render (double buffer).
+    Four consecutive frames (the mesh layer's temporal blend and the generators carry state from frame to frame) must be bit-identical
+    to the same four through snb_frame_host."""
+    m = common.model("small16x2")
+    d = m.desc(); assert snb.snb_set_model(ctx, C.byref(d)) == 0
+    sc = load_scene(snb, ctx, "c2")
+    rt = sc.rt.copy()
+    w, h = 160, 96
+    v = common.make_view(w, h)
+
+    def run(streamed):
+        assert snb.snb_seed_rng(ctx, 1999) == 0 and snb.snb_reset_accumulation(ctx) == 0
+        bufs = [(torch.empty((h, w, 4), dtype=torch.float32).pin_memory(), torch.empty((h, w), dtype=torch.float32).pin_memory()) for _ in range(2)]
+        frames = []
+        pending = []
+        for f in range(4):
+            slot = f & 1
+            if streamed:
+                if len(pending) == 2:                    # the slot's previous frame must be consumed before its buffers are reused
+                    s0 = pending.pop(0)
+                    assert snb.snb_frame_host_wait(ctx, s0) == 0
+                    frames.append((bufs[s0][0].numpy().copy(), bufs[s0][1].numpy().copy()))
+                rc = snb.snb_frame_host_async(ctx, C.byref(v), None, C.byref(rt), bufs[slot][0].data_ptr(), bufs[slot][1].data_ptr(), slot)
+                assert rc == 0, snb.snb_last_error(ctx)
+                pending.append(slot)
+            else:
+                rc = snb.snb_frame_host(ctx, C.byref(v), None, C.byref(rt), bufs[slot][0].data_ptr(), bufs[slot][1].data_ptr())
+                assert rc == 0, snb.snb_last_error(ctx)
+                frames.append((bufs[slot][0].numpy().copy(), bufs[slot][1].numpy().copy()))
+        for s0 in pending:
+            assert snb.snb_frame_host_wait(ctx, s0) == 0
+            frames.append((bufs[s0][0].numpy().copy(), bufs[s0][1].numpy().copy()))
+        return frames
+
+    a, b = run(False), run(True)
+    assert len(a) == len(b) == 4
+    assert a[0][0][..., 3].max() > 0.5 and not np.array_equal(a[0][0], a[1][0])          # frames differ from one another (temporal blend)
+    for (ra, da), (rb, db) in zip(a, b):
+        assert np.array_equal(ra, rb, equal_nan=True) and np.array_equal(da, db)
+    assert snb.snb_frame_host_wait(ctx, 2) != 0 and snb.snb_frame_host_async(ctx, C.byref(v), None, C.byref(rt), None, None, 0) != 0
