@@ -306,8 +306,10 @@ def run_ours(args, rank, local_rank, world):
         assert lib.snb_set_option(ctx, b"alt_schedule", b"external") == 0          # n_alive_j is a whole-frame quantity: summed over the ranks below
     n_rays_step = W * H * frames_per_step
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-    full_rgba = torch.empty((H, W, 4), device="cuda") if (split_frame and rank == 0) else None
-    full_depth = torch.empty((H, W), device="cuda") if (split_frame and rank == 0) else None
+    # rank 0's assembled frame, double-buffered: the D2H copy of frame i (e2e) runs on a copy stream while frame i + 1 is assembled into the other
+    full_bufs = [(torch.empty((H, W, 4), device="cuda"), torch.empty((H, W), device="cuda")) for _ in range(2)] if (split_frame and rank == 0) else None
+    full_rgba, full_depth = full_bufs[0] if full_bufs else (None, None)
+    asm = {"slot": 0, "copy_stream": torch.cuda.Stream() if (split_frame and rank == 0) else None, "done": [None, None], "pins": None}
     ev_a = torch.cuda.Event(enable_timing=True); ev_b = torch.cuda.Event(enable_timing=True)
     row_cost = torch.zeros(H, device="cuda", dtype=torch.float32) if split_frame else None
     stock_fb = torch.empty((H, W, 4), device="cuda") if stock else None
@@ -379,9 +381,21 @@ def run_ours(args, rank, local_rank, world):
         rgba, depth = eng.frame(sync=False, tile=band_tile(s))
         ev_b.record(stream)
         own = slice(s.x0 - s.hx0, s.x1 - s.hx0)
-        tiles.assemble_rows_on_root([rgba[own], depth[own]], bal.bounds, rank, world, dist, [full_rgba, full_depth])   # rgba + depth, 20 B/px, over NVLink
         if host is not None and rank == 0:
-            host[0].copy_(full_rgba, non_blocking=True); host[1].copy_(full_depth, non_blocking=True)
+            # e2e: streamed like the single-GPU form — assemble into buffer `slot`, copy it to pinned host memory on the copy stream
+            slot = asm["slot"]; asm["slot"] ^= 1
+            if asm["done"][slot] is not None:
+                stream.wait_event(asm["done"][slot])          # the slot's previous copy has left the device buffer
+                asm["done"][slot].synchronize()               # ... and its pinned host buffers may be overwritten
+            fr, fd = full_bufs[slot]
+            tiles.assemble_rows_on_root([rgba[own], depth[own]], bal.bounds, rank, world, dist, [fr, fd])
+            ready = torch.cuda.Event(); ready.record(stream)
+            with torch.cuda.stream(asm["copy_stream"]):
+                asm["copy_stream"].wait_event(ready)
+                asm["pins"][slot][0].copy_(fr, non_blocking=True); asm["pins"][slot][1].copy_(fd, non_blocking=True)
+                asm["done"][slot] = torch.cuda.Event(); asm["done"][slot].record(asm["copy_stream"])
+        else:
+            tiles.assemble_rows_on_root([rgba[own], depth[own]], bal.bounds, rank, world, dist, [full_rgba, full_depth])   # rgba + depth, 20 B/px, over NVLink
         if host is None and bal.due():
             if not args.alt_schedule:
                 sync_alt_schedule()
@@ -476,6 +490,8 @@ def run_ours(args, rank, local_rank, world):
         host = (pin_rgba, pin_depth)
         if split_frame and rank != 0:
             host = (None, None)
+        if split_frame and rank == 0:
+            asm["pins"] = [(pin_rgba, pin_depth), (torch.empty((H, W, 4), dtype=torch.float32).pin_memory(), torch.empty((H, W), dtype=torch.float32).pin_memory())]
         e2e_sync_s = None
         if eng is not None and not split_frame:
             # first the strictly synchronous call (snb_frame_host returns with the host buffers filled), reported as e2e.synchronous ...
@@ -586,7 +602,7 @@ def run_ours(args, rank, local_rank, world):
                        "present_stage": present},
             "e2e": {"value": n_rays_step * K / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d * frames_per_step, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s / K * 1e3,
                     "synchronous": ({"value": n_rays_step * K / e2e_sync_s / 1e6, "ms_per_step": e2e_sync_s / K * 1e3, "note": "snb_frame_host: returns with the host buffers filled, no overlap between frames"} if e2e_sync_s else None),
-                    "note": ("scene upload + snb_frame_host_async into two pinned host buffer pairs: a frame's device-to-host copy overlaps the next frame's render; all copies complete inside the timed region" if (eng is not None) else "stock render_nerf + D2H into pinned host buffers") if not split_frame else "scene upload + bands + assembly on rank 0 + D2H of the assembled rgba + depth frame into pinned host memory"},
+                    "note": ("scene upload + snb_frame_host_async into two pinned host buffer pairs: a frame's device-to-host copy overlaps the next frame's render; all copies complete inside the timed region" if (eng is not None) else "stock render_nerf + D2H into pinned host buffers") if not split_frame else "scene upload + bands + assembly on rank 0 + D2H of the assembled rgba + depth frame into pinned host memory (double-buffered: the copy overlaps the next frame; all copies complete inside the timed region)"},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": roof,

@@ -311,3 +311,26 @@ def test_oracle_present_properties():
     # (6) identity warp passed explicitly == default
     ident = [0, 0, 0, 1, 0, 0, 0, 0, 0, 1, 0, 1]
     np.testing.assert_array_equal(O.present(img, w, h, warp_x=ident, warp_y=ident), O.present(img, w, h))
+
+
+def test_engine_skip_frames_matches_walking_the_path():
+    """Engine.skip_frames(n) (frame-batch sharding: a rank walks past the frames other ranks render) leaves the camera-path position and the
+    animated objects where n plain iterations would, without touching a device."""
+    from synerfgine_b200 import scenes
+    from synerfgine_b200.testbed import Engine
+    a, b = Engine(), Engine()
+    for e in (a, b):
+        e.set_virtual_world_json(scenes.scene_json("c4"), scenes.mesh_dir()); e.path_frames = 24
+    assert a.is_playing and a.enable_animations
+    a.skip_frames(7); a.skip_frames(20)
+    sc = b.scene
+    between = max(1, 24 // max(sc.n_keyframes - 1, 1))
+    for _ in range(27):
+        b.current_frame += 1
+        if b.current_frame // between + 1 >= sc.n_keyframes:
+            b.current_frame = 0
+        sc.advance()
+    a.scene.refresh()
+    assert a.current_frame == b.current_frame
+    for i in range(sc.n_objects):
+        assert list(a.scene.objects[i].pos) == list(b.scene.objects[i].pos)
