@@ -10,9 +10,11 @@ mkdir -p "$OUT"
 cuobjdump -sass "$LIB" 2>/dev/null > /tmp/snb_all.sass
 # name -> substring of the mangled function name
 declare -A K=(
-  [k_nerf_raygen]="13k_nerf_raygen"
-  [k_nerf_march_fused_F2_alt_12warps]="18k_nerf_march_fusedILi2ELb1ELi12EE"
-  [k_nerf_march_fused_F2_stock_12warps]="18k_nerf_march_fusedILi2ELb0ELi12EE"
+  [k_nerf_raygen_pinhole]="13k_nerf_raygenILb0EE"
+  [k_nerf_raygen_camera_extras]="13k_nerf_raygenILb1EE"
+  [k_nerf_march_fused_F2_alt_12warps]="18k_nerf_march_fusedILi2ELb1ELi12ELb0EE"
+  [k_nerf_march_fused_F2_stock_12warps]="18k_nerf_march_fusedILi2ELb0ELi12ELb0EE"
+  [k_nerf_march_fused_F2_alt_12warps_lockstep]="18k_nerf_march_fusedILi2ELb1ELi12ELb1EE"
   [k_nerf_march_ws_F2_alt]="15k_nerf_march_wsILi2ELb1EE"
   [k_network_inference_tc_F2]="22k_network_inference_tcILi2EE"
   [k_write_normals]="15k_write_normals"
@@ -26,6 +28,10 @@ declare -A K=(
   [k_alt_verify]="12k_alt_verify"
   [k_alt_begin_pass]="16k_alt_begin_pass"
   [k_grid_scales]="13k_grid_scales"
+  [k_lock_begin]="12k_lock_begin"
+  [k_lock_next]="11k_lock_next"
+  [k_lbvh_topology]="15k_lbvh_topology"
+  [k_bvh_fit]="9k_bvh_fit"
 )
 SUMMARY="$OUT/SUMMARY.txt"
 echo "# SASS listings of $(basename "$LIB") ($(date -u +%F)); instruction counts and tensor / TMA / TMEM mnemonics per kernel" > "$SUMMARY"

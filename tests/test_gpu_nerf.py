@@ -491,3 +491,38 @@ def test_lockstep_prefix_equals_the_speculative_schedule(snb, orc, ctx, kind, w,
     finally:
         snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_auto_lockstep", b"1"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152")
         snb.snb_set_alt_schedule(ctx, None, 0)
+
+
+def test_two_contexts_on_two_devices_in_one_process(snb):
+    """launch set-up (dynamic shared-memory opt-in, occupancy) is cached per CONTEXT, not per process, so a second context on
+    another device renders like the first. Needs two GPUs (skipped on a single-GPU box)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    m = common.model("small16x2")
+    v = common.make_view(128, 96)
+    rt = common.default_rt(show_shadow_on_nerf=0)
+    frames = []
+    ctxs = []
+    try:
+        for devi in (0, 1):
+            c = C.c_void_p(); assert snb.snb_create(devi, None, C.byref(c)) == 0
+            ctxs.append(c)
+            d = m.desc(); assert snb.snb_set_model(c, C.byref(d)) == 0
+        for devi, c in enumerate(ctxs):                      # both contexts alive at the same time
+            with torch.cuda.device(devi):
+                fb = torch.zeros((96, 128, 4), device=f"cuda:{devi}"); depth = torch.zeros((96, 128), device=f"cuda:{devi}")
+                pos = torch.zeros((96, 128, 3), device=f"cuda:{devi}"); nrm = torch.zeros((96, 128, 3), device=f"cuda:{devi}")
+                torch.cuda.synchronize(devi)
+                for _ in range(2):
+                    rc = snb.snb_render_nerf_with_buffers(c, C.byref(v), None, C.byref(rt), 1, fb.data_ptr(), depth.data_ptr(), pos.data_ptr(), nrm.data_ptr())
+                    assert rc == 0, snb.snb_last_error(c)
+                assert snb.snb_sync(c) == 0
+                sfb = torch.zeros((96, 128, 4), device=f"cuda:{devi}"); sd = torch.zeros((96, 128), device=f"cuda:{devi}")
+                torch.cuda.synchronize(devi)
+                assert snb.snb_render_nerf(c, C.byref(v), None, 1, sfb.data_ptr(), sd.data_ptr()) == 0 and snb.snb_sync(c) == 0
+                frames.append((fb.cpu().numpy(), sfb.cpu().numpy()))
+    finally:
+        for c in ctxs:
+            snb.snb_destroy(c)
+    assert frames[0][0][..., 3].max() > 0.5
+    assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
