@@ -252,6 +252,10 @@ int snb_frame_host_wait(snb_ctx* ctx, int32_t slot);
 /* Per-ray march sample sequence: t, dt, cell = mip << 24 | morton (0xFFFFFFFF padding), n per ray. */
 int snb_march_trace(snb_ctx* ctx, const snb_view* view, uint32_t max_samples, float* t_dev, float* dt_dev, uint32_t* cell_dev, uint32_t* n_dev,
                     float* origin_dir_dev /* n x 6 or NULL */);
+/* The same sequence as recorded by the FUSED MARCH KERNEL itself (not a separate trace kernel): after this call snb_render_nerf (stock
+ * path, march=lane) writes, per tile pixel, t and cell of every sample it evaluates (first `cap` per ray; n x cap arrays) and the number
+ * of samples (n array, must be zeroed by the caller). NULL arrays switch the tap off. */
+int snb_set_sample_tap(snb_ctx* ctx, float* t_dev, uint32_t* cell_dev, uint32_t* n_dev, uint32_t cap);
 /* ≙ NerfNetwork::inference_mixed_precision (nerf_network.h:105-139): coords n x 7 fp32 → n x 4 fp16 (rgb, sigma);
  * optional features n x 32 fp16 and hash indices n x (n_levels * 8). */
 int snb_network_inference(snb_ctx* ctx, const float* coords_dev, uint64_t n, uint16_t* out_dev, uint16_t* features_dev, uint32_t* hash_idx_dev);

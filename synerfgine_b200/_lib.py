@@ -107,6 +107,7 @@ SIGNATURES = {
     "snb_bvh_refit_dev": (C.c_int, [vp, vp, vp, i32]),
     "snb_bvh_refit_dev_noalloc": (C.c_int, [vp, vp, vp, i32]),
     "snb_update_object_triangles": (C.c_int, [vp, u32, pf32]),
+    "snb_set_sample_tap": (C.c_int, [vp, vp, vp, vp, u32]),
     "snb_set_camera_ex": (C.c_int, [vp, C.POINTER(CameraEx)]),
     "snb_set_envmap": (C.c_int, [vp, pf32, i32, i32]),
     "snb_camera_log_lerp": (C.c_int, [pf32, pf32, f32, pf32]),

@@ -91,6 +91,8 @@ struct snb_ctx {
 	int bvh_max_depth = 0;             // deepest leaf of the last device builds (the traversal stack holds 32 entries)
 	snb::LbvhScratch lbvh;
 	snb::DevBuf d_tris_in, d_bvh_depth;
+	// parity tap of the fused march on the stock path (snb_set_sample_tap): caller-owned device arrays
+	float* tap_t = nullptr; uint32_t* tap_cell = nullptr; uint32_t* tap_n = nullptr; uint32_t tap_cap = 0;
 	// stock-path camera extras (snb_set_camera_ex / snb_set_envmap); cam_ex.enabled == 0 and no envmap: plain pinhole ray generation
 	snb::CameraEx cam_ex = {};
 	bool has_cam_ex = false;

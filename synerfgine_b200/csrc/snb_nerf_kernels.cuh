@@ -33,6 +33,8 @@ struct NerfOut {                     // tile-sized output buffers
 	float4* fb;                      // rgba
 	float* depth;
 	float* positions;                // xyz per pixel (alt path) or nullptr
+	// parity tap of the fused march (snb_set_sample_tap; all nullptr normally): per tile pixel the samples the kernel itself evaluates
+	float* tap_t; uint32_t* tap_cell; uint32_t* tap_n; uint32_t tap_cap;
 };
 
 // ---- batch schedule of the sng compositor ------------------------------------------------------------------------------------
@@ -362,6 +364,19 @@ __device__ __noinline__ void clear_pixel(const DevView& view, const NerfOut& out
 	if (out.positions) { out.positions[l * 3 + 0] = 0.0f; out.positions[l * 3 + 1] = 0.0f; out.positions[l * 3 + 2] = 0.0f; }
 }
 
+// Parity tap (snb_set_sample_tap): sample number `ord` of pixel idx as the march kernel evaluates it. Out of line: the hot loop keeps its registers.
+__device__ __noinline__ void tap_sample(const NerfOut& out, const DevView& view, uint32_t idx, uint32_t ord, v3 sp, float t, uint32_t min_mip, uint32_t max_mip) {
+	const int l = tile_local_index(view, idx);
+	if (ord < out.tap_cap) {
+		uint32_t mip = mip_of(sp);
+		if (mip < min_mip) mip = min_mip;
+		if (mip > max_mip) mip = max_mip;
+		out.tap_t[(size_t)l * out.tap_cap + ord] = t;
+		out.tap_cell[(size_t)l * out.tap_cap + ord] = (mip << 24) | (cascade_cell(sp, mip) & 0xFFFFFFu);
+	}
+	out.tap_n[l] = ord + 1u;
+}
+
 // ---- the persistent fused kernel -----------------------------------------------------------------------------------
 // grid = SMs x SNB_LANE_CTAS (2), block = SNB_LANE_WARPS (12) warps; dynamic smem (kLaneSmemBytes, 70 KB) = fragment-ordered
 // MLP weights (20 KB, shared by the CTA's warps) + per-warp staging tile (3.5 KB) + per-warp output tile (256 B) + level
@@ -535,6 +550,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 			const float dt = step_size_call(t, env.st);
 			wpos = (o + d * t - model.train_aabb.lo) / aabb_diag;   // warp_position
 			wdt = dt_warp(dt);
+			if constexpr (!ALT) { if (out.tap_t) tap_sample(out, view, idx, step_i - 1u + (uint32_t)k, o + d * t, t, env.min_mip, env.max_mip); }   // uniform; off outside the parity test
 			t += dt;
 			// -- hash-grid gather straight into this lane's row of the staging tile ---------------------------------------
 			encode_position_to_row<F, false>(s_levels, wpos, tile + lane * kTileStrideH, nullptr);

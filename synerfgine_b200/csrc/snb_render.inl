@@ -104,6 +104,8 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	SNB_CUDA(c, cudaMemsetAsync(c->d_qctl.p, 0, 16, c->stream));
 	SNB_CUDA(c, cudaMemsetAsync(c->d_counters.p, 0, 2 * sizeof(NerfCounters), c->stream));   // counters + pipeline-balance cycles of the ws march
 	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
+	out.tap_t = nullptr; out.tap_cell = nullptr; out.tap_n = nullptr; out.tap_cap = 0;
+	if (!alt && c->tap_t && c->march_variant == 3) { out.tap_t = c->tap_t; out.tap_cell = c->tap_cell; out.tap_n = c->tap_n; out.tap_cap = c->tap_cap; }
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches_x = (dv.tw + 7) / 8, patches_y = (dv.th + 3) / 4;
 	const int patches = patches_x * patches_y;

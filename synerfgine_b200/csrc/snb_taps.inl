@@ -159,6 +159,15 @@ int snb_set_alt_schedule(snb_ctx* c, const uint8_t* steps, uint32_t n) {
 	return SNB_OK;
 }
 
+// The march kernel's own samples: the following snb_render_nerf calls (stock path, lane march) record, per tile pixel, t and
+// cell = mip << 24 | Morton index of every sample k_nerf_march_fused evaluates (first `cap` per ray) and the count. NULL clears the tap.
+int snb_set_sample_tap(snb_ctx* c, float* t_dev, uint32_t* cell_dev, uint32_t* n_dev, uint32_t cap) {
+	if (!c) return SNB_ERR_ARG;
+	if (!t_dev || !cell_dev || !n_dev || cap == 0) { c->tap_t = nullptr; c->tap_cell = nullptr; c->tap_n = nullptr; c->tap_cap = 0; return SNB_OK; }
+	c->tap_t = t_dev; c->tap_cell = cell_dev; c->tap_n = n_dev; c->tap_cap = cap;
+	return SNB_OK;
+}
+
 int snb_set_camera_ex(snb_ctx* c, const snb_camera_ex* ex) {
 	if (!c) return SNB_ERR_ARG;
 	if (!ex) { c->has_cam_ex = false; c->cam_ex = CameraEx{}; return SNB_OK; }

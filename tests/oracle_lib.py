@@ -150,6 +150,42 @@ def frame(model_desc, view, scene, rt, rng_seed=1999, n_frames=1):
     return out
 
 
+class FrameLoop:
+    """Oracle of consecutive Engine::frame calls (syn_px_scale 1) with a moving camera and world: generator states carry from frame to
+    frame (Engine::resize seeds them once), the mesh layer's rays and temporal blend restart whenever `reset` is set
+    (RayTracer::reset_accumulation: a camera move, engine.cu:366-369, or Engine::update_world_objects, :80-127)."""
+
+    def __init__(self, w, h, rng_seed=1999):
+        self.lib = load()
+        self.w, self.h, self.n = w, h, w * h
+        n = self.n
+        self.origins = np.zeros((n, 3), np.float32); self.dirs = np.zeros((n, 3), np.float32)
+        self.acc_rgba = np.zeros((n, 4), np.float32); self.acc_depth = np.zeros(n, np.float32)
+        self.rng_syn = np.zeros((n, 6), np.uint32); self.lib.orc_xorwow_states(rng_seed, n, P(self.rng_syn, pu32))
+        self.rng_nerf = self.rng_syn.copy()
+        self.fresh = True
+
+    def step(self, model_desc, view, scene, rt, reset):
+        lib, n, w, h = self.lib, self.n, self.w, self.h
+        if reset or self.fresh:
+            lib.orc_syn_init_rays(C.byref(view), P(self.origins), P(self.dirs), None, None, P(self.acc_rgba), P(self.acc_depth))
+            self.fresh = False
+        lib.orc_syn_raytrace(n, P(self.origins), P(self.dirs), C.byref(view), C.byref(model_desc), scene.objects, scene.n_objects, scene.materials, scene.n_materials,
+                             scene.lights, scene.n_lights, C.byref(rt), P(self.rng_syn, pu32), P(self.acc_rgba), P(self.acc_depth))
+        fb = np.zeros((n, 4), np.float32); depth = np.zeros(n, np.float32); pos = np.zeros((n, 3), np.float32); normals = np.zeros((n, 3), np.float32)
+        shadow = np.ones(n, np.float32)
+        if rt.show_nerf:
+            lib.orc_render_nerf(C.byref(model_desc), C.byref(view), 1, 1, 8, P(fb), P(depth), P(pos), None)
+            lib.orc_write_normals(w, h, P(pos), P(normals))
+            if rt.show_shadow_on_nerf:
+                lib.orc_shade_nerf_shadows(w, h, C.byref(model_desc), P(pos), P(normals), scene.objects, scene.n_objects, scene.lights, scene.n_lights,
+                                           C.byref(rt), P(self.rng_nerf, pu32), 1, P(fb), P(shadow))
+        final = np.zeros((n, 4), np.float32); final_depth = np.zeros(n, np.float32)
+        lib.orc_overlay(w, h, 1, P(self.acc_rgba), P(self.acc_depth), P(fb), P(depth), rt.show_nerf, 1, rt.tonemap_curve, rt.exposure, rt.depth_offset, P(final), P(final_depth))
+        return {"final": final.reshape(h, w, 4), "final_depth": final_depth.reshape(h, w), "syn_depth": self.acc_depth.copy().reshape(h, w),
+                "nerf_rgba": fb.reshape(h, w, 4), "shadow": shadow.reshape(h, w)}
+
+
 def present(rgba, out_w, out_h, clear=(0.0, 0.0, 0.0), warp_x=None, warp_y=None):
     """Oracle present stage (FXAA blit + blend + RGB8): rgba [h, w, 4] float32 -> uint8 [out_h, out_w, 3], rows top-down."""
     lib = load()

@@ -526,3 +526,38 @@ def test_two_contexts_on_two_devices_in_one_process(snb):
             snb.snb_destroy(c)
     assert frames[0][0][..., 3].max() > 0.5
     assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+
+
+@pytest.mark.parametrize("kind,w,h", [("small16x2", 128, 96), ("big16x2", 96, 64)])
+def test_fused_march_kernel_samples_equal_the_trace(snb, orc, ctx, kind, w, h):
+    """k_nerf_march_fused ITSELF (not the separate trace kernel) reports the samples it evaluates (snb_set_sample_tap):
+    per ray they are a prefix of the untruncated sequence of snb_march_trace — t bit for bit, same cascade cell — which
+    test_march_samples_bit_exact pins to the oracle; the prefix ends where the compositor terminated the ray."""
+    m = common.model(kind)
+    set_model(snb, ctx, m)
+    assert snb.snb_set_option(ctx, b"march", b"lane") == 0
+    cam = common.camera_matrix(zoom=2.5) if kind == "big16x2" else None
+    v = common.make_view(w, h, cam=cam, spp=2, snap=0)
+    n, S = w * h, 48
+    t, dt, cell, cnt = dev((n, S), torch.float32), dev((n, S), torch.float32), dev((n, S), torch.int32), dev((n,), torch.int32)
+    assert snb.snb_march_trace(ctx, C.byref(v), S, t.data_ptr(), dt.data_ptr(), cell.data_ptr(), cnt.data_ptr(), None) == 0 and snb.snb_sync(ctx) == 0
+    ft, fc, fn = dev((n, S), torch.float32), dev((n, S), torch.int32), dev((n,), torch.int32)
+    fb, depth = dev((h, w, 4), torch.float32), dev((h, w), torch.float32)
+    assert snb.snb_set_sample_tap(ctx, ft.data_ptr(), fc.data_ptr(), fn.data_ptr(), S) == 0
+    try:
+        assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0 and snb.snb_sync(ctx) == 0
+    finally:
+        assert snb.snb_set_sample_tap(ctx, None, None, None, 0) == 0
+    t, cell, cnt = t.cpu().numpy(), cell.cpu().numpy(), cnt.cpu().numpy()
+    ft, fc, fn = ft.cpu().numpy(), fc.cpu().numpy(), fn.cpu().numpy()
+    assert (fn > 0).sum() > 200 and np.array_equal(fn > 0, cnt > 0)
+    k = np.minimum(np.minimum(fn, cnt), S)
+    assert (fn <= np.where(cnt < S, cnt, fn)).all()                   # never more samples than the sequence holds
+    mask = np.arange(S)[None, :] < k[:, None]
+    assert np.array_equal(ft.view(np.uint32)[mask], t.view(np.uint32)[mask])
+    assert np.array_equal(fc[mask], cell[mask])
+    assert (fn < cnt).sum() > 50, "degenerate test: no ray was terminated by the compositor"
+    # the tap is off again: the next render leaves the arrays alone
+    before = ft.copy()
+    assert snb.snb_render_nerf(ctx, C.byref(v), None, 1, fb.data_ptr(), depth.data_ptr()) == 0 and snb.snb_sync(ctx) == 0
+    assert np.array_equal(before, ft)

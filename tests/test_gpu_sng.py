@@ -443,3 +443,46 @@ def test_streamed_host_frames_equal_the_synchronous_ones(snb, ctx):
     for (ra, da), (rb, db) in zip(a, b):
         assert np.array_equal(ra, rb, equal_nan=True) and np.array_equal(da, db)
     assert snb.snb_frame_host_wait(ctx, 2) != 0 and snb.snb_frame_host_async(ctx, C.byref(v), None, C.byref(rt), None, None, 0) != 0
+
+
+def test_c4_consecutive_animated_frames_match_oracle(snb, orc):
+    """BASELINE config C4 in small: three animated objects and a keyframe camera path, four CONSECUTIVE iterations of the frame loop
+    (Engine.step: CamPath advance, VirtualObject / Light next_frame, accumulation reset, render) against the oracle run frame by frame
+    with the same cameras and world states. Generator states carry across frames on both sides, so frame k is only right if frames
+    0..k-1 drew the same random numbers. Bar as test_full_frame_matches_oracle: >= 50 dB over the finite values, <= 1 % of pixels
+    over 1e-2, NaN pixels (directional light: pow of a negative mean, kept for parity) in the same places."""
+    from synerfgine_b200.testbed import Engine, Testbed
+    w, h = 96, 64
+    m = common.model("small16x2")
+    tb = Testbed()
+    try:
+        tb.set_model(m)
+        common.use_device_grid_scales(snb, tb.ctx)
+        eng = Engine()
+        eng.set_virtual_world_json(scenes.scene_json("c4"), scenes.mesh_dir())
+        eng.path_frames = 24
+        eng.init(w, h, tb)
+        assert eng.is_playing and eng.enable_animations
+        loop = O.FrameLoop(w, h)
+        d = m.desc()
+        cams, worst = [], 99.0
+        for f in range(4):
+            rgba, depth = eng.step()
+            a, da = rgba.cpu().numpy().copy(), depth.cpu().numpy().copy()
+            v = tb.make_view(w, h, eng.frame_index - 1)
+            cams.append(np.asarray(tb.camera_matrix, np.float32).copy())
+            ref = loop.step(d, v, eng.scene, eng.rt, reset=True)
+            assert (ref["syn_depth"] < 1000).mean() > 0.01 and (ref["nerf_rgba"][..., 3] > 0.5).mean() > 0.05
+            both_nan = np.isnan(a) & np.isnan(ref["final"])
+            dd = np.where(both_nan, 0.0, np.abs(a - ref["final"])); dd = np.where(np.isnan(dd), np.inf, dd)
+            bad = dd.max(-1) > 1e-2
+            ps = finite_psnr(a, ref["final"])
+            worst = min(worst, ps)
+            print(f"[c4 frame {f}] psnr {ps:.1f} dB, pixels over 1e-2: {int(bad.sum())} of {w * h}, NaN pixels {int(np.isnan(a).any(-1).sum())}")
+            assert bad.sum() <= 0.01 * w * h, (f, int(bad.sum()))
+            assert ps >= 50.0, (f, ps)
+            hit = ref["syn_depth"] < 1000
+            np.testing.assert_allclose(da[hit], ref["final_depth"][hit], rtol=1e-4, atol=1e-4)
+        assert not np.array_equal(cams[0], cams[1]) and not np.array_equal(cams[1], cams[2])      # the camera did follow the path
+    finally:
+        tb.close()
