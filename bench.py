@@ -446,6 +446,7 @@ def run_ours(args, rank, local_rank, world):
         launches0 = tb.launch_count()
         sampler = ClockSampler(local_rank); sampler.start()
         step_ms, march_ms, stage_acc, samples, rays, march_stats, alt, pass_log = [], [], {}, 0, 0, {}, None, []
+        reused = 0
         for _ in range(K):
             flush.zero_()                                  # L2 flush between timed iterations (outside the event pair)
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
@@ -457,7 +458,7 @@ def run_ours(args, rank, local_rank, world):
             st = tb.stage_ms(); march_ms.append(st["nerf_march"])
             for k_, v_ in st.items():
                 stage_acc[k_] = stage_acc.get(k_, 0.0) + v_ / K
-            c = tb.counters(); samples += c["samples"]; rays += c["rays"]
+            c = tb.counters(); samples += c["samples"]; rays += c["rays"]; reused += c.get("reused", 0)
             ast_ = (C.c_uint32 * 132)(); lib.snb_get_alt_status(ctx, ast_); pass_log.append((int(ast_[0]), int(ast_[1])))
         torch.cuda.synchronize()
         if world > 1:
@@ -595,7 +596,8 @@ def run_ours(args, rank, local_rank, world):
             "config": {"workload": cfg["workload"], "name": args.config, "resolution": [W, H], "frames_per_step": frames_per_step, "march": tb_march,
                        "parallelism": (f"{world} row bands, halo {halo}px, edges balanced from measured frame times: {bal.bounds} ({bal.changes} moves); rgba + depth assembled on rank 0 (NCCL p2p, 20 B/px)" if split_frame
                                        else (f"{cfg['frames']} frames sharded over {world} ranks ({args.batch_assign}{': chunk edges ' + str(batch_bounds) if batch_bounds else ''}), whole frames, no halo" if cfg.get("batch") else "single GPU")),
-                       "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples_per_launch, "rays_marched_per_frame": rays_per_launch,
+                       "l2": "256 MB buffer written between timed iterations", "samples_per_frame": samples_per_launch, "samples_reused_per_frame": reused / max(1, K * frames_per_step) * (world if cfg.get("batch") else 1),
+                       "samples_note": "samples_per_frame = network evaluations (hash gather + both MLPs) the march performs; samples_reused = samples the reference evaluates a second time after its compositor's rewind and this kernel composites from the first evaluation (option dup_reuse); their sum is the reference's sample count", "rays_marched_per_frame": rays_per_launch,
                        "march_stats_last_frame": march_stats, "alt_schedule": alt, "ms_per_frame": total_ms / nframes,
                        "stage_ms": {k_: round(v_, 4) for k_, v_ in stage_acc.items()},
                        "step_ms_min_med_p95_max": [round(float(np.min(step_ms)), 4), round(float(np.median(step_ms)), 4), round(float(np.percentile(step_ms, 95)), 4), round(float(np.max(step_ms)), 4)],

@@ -168,6 +168,11 @@ const char* snb_version(void);
  *                    the batches shorter than 8 in lock step, one per launch, from parked ray states: exact in one pass. lockstep: always.
  *                    "alt_auto_lockstep" = "0" keeps auto on verified speculation only)
  *   "alt_batch"    = "1".."8"        batch length of alt_schedule = fixed
+ *   "dup_reuse"    = "1" (default) | "0"   sng path: the compositor's rewind (composite_kernel_nerf_alt, src/testbed_nerf.cu:574) makes the first
+ *                    sample of every batch the last sample of the previous one again — the reference gathers and evaluates it a second time
+ *                    at a position that differs by the rounding of the rewind. 1: its network output is re-used (position, dt, depth and
+ *                    termination are computed as always): a quarter fewer network evaluations on a 1080p frame, results within the
+ *                    frame tolerance (>= 50 dB, counted pixels over 1e-2); 0: every sample goes through the network (exact counts)
  *   "alt_target_queries" = "2097152" target_n_queries of NerfTracer::trace_alt (src/testbed_nerf.cu:2188); tests lower it to exercise short batches on small frames
  * Implementation selectors (A/B measurements; frames are bit-identical unless noted):
  *   "march"      = "lane" (default: one ray per lane, MLPs on warp-level mma.sync) | "ws" (warp-specialised pipeline, MLPs on tcgen05 tensor
@@ -267,7 +272,8 @@ int snb_rng_tap(snb_ctx* ctx, uint64_t seed, uint32_t n, uint32_t n_uniform, uin
 /* Per-level grid scales of the current model as the device evaluates tcnn's grid_scale (exp2f = MUFU.EX2, one FFMA; common_device.h:841-845).
  * Returns the number of levels written or a negative status. */
 int snb_get_grid_scales(snb_ctx* ctx, float* out_host, uint32_t cap);
-/* Counters of the last NeRF render: [0] network samples, [1] rays launched, [2] rays that hit, [3] march batches. */
+/* Counters of the last NeRF render: [0] network samples evaluated, [1] rays launched, [2] rays that hit, [3] samples composited from a
+ * re-used network output (option dup_reuse; [0] + [3] = samples composited = what the reference evaluates). */
 int snb_get_counters(snb_ctx* ctx, uint64_t* out4_host);
 /* Scheduling statistics of the last NeRF march (instrumentation; SURVEY.md 8d "device counters"): [0] pool iterations summed
  * over CTAs, [1] empty-space DDA steps, [2] search passes (warp level), [3] CTAs of the persistent grid. */

@@ -61,7 +61,7 @@ struct AltState {                     // device-resident, one per context
 // costs a few batches, not a frame. As soon as a committed length is 8 (n_alive <= target / 8, and it only falls) the rest of the march
 // is one free-running launch from the checkpoint. Per ray the arithmetic is that of the speculative path, so frames are bit-identical.
 constexpr int kLockChunk = 1;
-struct RayPark { float4 rgba; float t, depth, max_weight; uint32_t step_i; };   // 32 B per queued ray, indexed by queue position
+struct RayPark { float4 rgba; float t, depth, max_weight; uint32_t step_i; uint32_t k, dead, pad0, pad1; };   // 48 B per queued ray, indexed by queue position
 struct LockState {                     // device-resident, behind AltState
 	uint32_t cur_batch;                // checkpoint: batches < cur_batch are committed
 	uint32_t stop_batch;               // the attempt in flight covers [cur_batch, stop_batch)
@@ -82,6 +82,7 @@ struct AltCtl {
 	RayPark* park[2];                 // ping-pong: the checkpoint's states / the states the attempt in flight parks
 	uint32_t* lists[2];               // ping-pong lists of queue positions of the rays still alive
 	uint32_t phase;                   // 0 = not phased, 1 = prefix attempt (one chunk, then park), 2 = final launch (run to completion)
+	uint32_t reuse_dup;               // re-use the network output for the sample the rewind makes the compositor evaluate twice (option dup_reuse)
 };
 SNB_HD uint32_t alt_steps_for(uint32_t target, uint32_t n_alive) {
 	uint32_t s = n_alive ? target / n_alive : 8u;
@@ -470,7 +471,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 #pragma unroll
 		for (int i = 0; i < kTileStrideH * 2 / 16; ++i) row[i] = make_uint4(0, 0, 0, 0);
 	}
-	uint32_t n_samples = 0, n_hits = 0, n_launched = 0;
+	uint32_t n_samples = 0, n_hits = 0, n_launched = 0, n_reused = 0;
 
 	auto finish = [&]() {
 		alive = false;
@@ -502,8 +503,9 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 					qpos = qp;
 					if (resume) {   // compositor state as it was at the end of batch batch0 - 1
 						const RayPark pk = park_in[qp];
-						rgba = pk.rgba; t = pk.t; depth = pk.depth; max_weight = pk.max_weight; step_i = pk.step_i;
+						rgba = pk.rgba; t = pk.t; depth = pk.depth; max_weight = pk.max_weight; step_i = pk.step_i; k = (int)pk.k;
 						batch = batch0; batch_steps = batch0 < (uint32_t)kAltSched ? s_sched[batch0] : (uint32_t)kBatchSteps;
+						if (pk.dead) alive = false;   // counted alive at the start of this batch, ended while its re-composited sample was folded in
 					}
 				} else {
 					if (count_batches) atomicAdd(&s_hist[0], 1u);
@@ -569,46 +571,72 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		if (valid) {
 			++n_samples;
 			const __half2 rg = u2h2(net.x), bs = u2h2(net.y);
-			const v3 pos = model.train_aabb.lo + wpos * aabb_diag;   // unwarp_position
-			const float T = 1.f - rgba.w;
-			const float dt = dt_unwarp(wdt);
-			const float alpha = 1.f - __expf(-act_density(__high2float(bs), model.density_act) * dt);
-			const float weight = alpha * T;
-			v3 rgb = mk3(act_rgb(__low2float(rg), model.rgb_act), act_rgb(__high2float(rg), model.rgb_act), act_rgb(__low2float(bs), model.rgb_act));
-			if (!ALT) {
-				if (render_mode == 3) rgb = (pos - 0.5f) / 2.0f + 0.5f;
-				else if (render_mode == 4) rgb = splat3(dot(cam_fwd, pos - o) * 1.0f);
-			}
-			rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
-			if (ALT) {
-				depth = dot(cam_fwd, pos - view.cam.c3);
-				if (weight > max_weight) max_weight = weight;
-			} else if (weight > max_weight) {
-				max_weight = weight;
-				depth = dot(cam_fwd, pos - view.cam.c3);
-			}
-			if (rgba.w > (1.0f - model.min_transmittance)) {
-				const float inv_a = 1.0f / rgba.w;
-				rgba.x *= inv_a; rgba.y *= inv_a; rgba.z *= inv_a; rgba.w *= inv_a;
-				fin = true;
-			} else if (++k == (int)batch_steps) {
+			const float sigma = act_density(__high2float(bs), model.density_act);
+			const v3 rgb_net = mk3(act_rgb(__low2float(rg), model.rgb_act), act_rgb(__high2float(rg), model.rgb_act), act_rgb(__low2float(bs), model.rgb_act));
+			// One trip per composited sample. A second trip happens only with alt.reuse_dup (sng path): the compositor's rewind makes the first
+			// sample of the next batch the last sample of this one again (same position up to the rounding of the rewind), so its network
+			// output is re-used instead of being gathered and evaluated a second time; position, dt, depth and all bookkeeping of that
+			// sample are computed as always.
+			bool parking = false;
+#pragma unroll 1
+			for (int rep = 0; ; ++rep) {
+				const v3 pos = model.train_aabb.lo + wpos * aabb_diag;   // unwarp_position
+				const float T = 1.f - rgba.w;
+				const float dt = dt_unwarp(wdt);
+				const float alpha = 1.f - __expf(-sigma * dt);
+				const float weight = alpha * T;
+				v3 rgb = rgb_net;
+				if (!ALT) {
+					if (render_mode == 3) rgb = (pos - 0.5f) / 2.0f + 0.5f;
+					else if (render_mode == 4) rgb = splat3(dot(cam_fwd, pos - o) * 1.0f);
+				}
+				rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
+				if (ALT) {
+					depth = dot(cam_fwd, pos - view.cam.c3);
+					if (weight > max_weight) max_weight = weight;
+				} else if (weight > max_weight) {
+					max_weight = weight;
+					depth = dot(cam_fwd, pos - view.cam.c3);
+				}
+				if (rgba.w > (1.0f - model.min_transmittance)) {
+					const float inv_a = 1.0f / rgba.w;
+					rgba.x *= inv_a; rgba.y *= inv_a; rgba.z *= inv_a; rgba.w *= inv_a;
+					fin = true;
+					break;
+				}
+				if (parking) { ++k; break; }                          // the folded sample of a ray that is about to park (its batch length is not known yet)
+				if (++k != (int)batch_steps) break;
 				// batch boundary: the sng compositor rewinds t to the last composited sample
 				if (ALT) t = depth / dot(cam_fwd, d);
 				k = 0;
 				step_i += batch_steps;
-				if (step_i >= kMarchIter) alive = false;         // iteration budget exhausted: ray is dropped, not written
-				else {
-					++batch;
-					if (PH && batch == stop_batch) {
-						// lock-step prefix: park at the batch boundary; the number of parked rays is n_alive of the next batch
-						RayPark pk; pk.rgba = rgba; pk.t = t; pk.depth = depth; pk.max_weight = max_weight; pk.step_i = step_i;
-						park_out[qpos] = pk;
-						list_out[atomicAdd(&alt.lk->n_out, 1u)] = qpos;
-						alive = false;
-					}
-					else if (batch < (uint32_t)kAltSched) { batch_steps = s_sched[batch]; if (count_batches) atomicAdd(&s_hist[batch], 1u); }
-					else batch_steps = ALT && alt.fixed_steps ? alt.fixed_steps : kBatchSteps;
+				if (step_i >= kMarchIter) { alive = false; break; }         // iteration budget exhausted: ray is dropped, not written
+				++batch;
+				const uint32_t prev_steps = batch_steps;
+				if (PH && batch == stop_batch) {
+					// lock-step prefix: the ray is alive at the start of batch `stop`: count it and list it now; its state is parked below,
+					// after the sample the rewind repeats has been folded in (exactly what the free-running path does at this point)
+					list_out[atomicAdd(&alt.lk->n_out, 1u)] = qpos;
+					parking = true;
 				}
+				else if (batch < (uint32_t)kAltSched) { batch_steps = s_sched[batch]; if (count_batches) atomicAdd(&s_hist[batch], 1u); }
+				else batch_steps = ALT && alt.fixed_steps ? alt.fixed_steps : kBatchSteps;
+				// lengths never fall along a march, so a batch that follows one of >= 2 samples cannot end with the folded sample
+				if (!ALT || !alt.reuse_dup || rep != 0 || prev_steps < 2u) break;
+				// the re-composited sample of the new batch, at the rewound t (what the search phase + sample position would find next iteration)
+				const v3 p2 = o + d * t;
+				if (t >= kMaxDepth || !in_render_box(p2, env)) break;
+				if (env.bitfield && !cell_occupied_xyz(p2, env.bits_xyz, clamp_mip(mip_of(p2), env))) break;   // the rewind left the cell: a new sample after all
+				const float dt2 = step_size_call(t, env.st);
+				wpos = (p2 - model.train_aabb.lo) / aabb_diag;
+				wdt = dt_warp(dt2);
+				t += dt2;
+				++n_reused;
+			}
+			if (PH && parking) {
+				RayPark pk; pk.rgba = rgba; pk.t = t; pk.depth = depth; pk.max_weight = max_weight; pk.step_i = step_i; pk.k = (uint32_t)k; pk.dead = fin ? 1u : 0u; pk.pad0 = 0; pk.pad1 = 0;
+				park_out[qpos] = pk;
+				if (!fin) alive = false;       // fin: finish() writes the pixel at the top of the next iteration
 			}
 		}
 	}
@@ -619,6 +647,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		n_samples += __shfl_xor_sync(0xFFFFFFFFu, n_samples, s);
 		n_hits += __shfl_xor_sync(0xFFFFFFFFu, n_hits, s);
 		n_launched += __shfl_xor_sync(0xFFFFFFFFu, n_launched, s);
+		n_reused += __shfl_xor_sync(0xFFFFFFFFu, n_reused, s);
 	}
 	if (PH && alt.phase == 1) {   // a prefix attempt: its counts become final only when k_lock_next commits the chunk
 		if (lane == 0) { atomicAdd(&alt.lk->pend_samples, (unsigned long long)n_samples); atomicAdd(&alt.lk->pend_hits, (unsigned long long)n_hits); }
@@ -626,6 +655,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		atomicAdd(&counters->samples, (unsigned long long)n_samples);
 		atomicAdd(&counters->hits, (unsigned long long)n_hits);
 		atomicAdd(&counters->rays, (unsigned long long)n_launched);
+		if (n_reused) atomicAdd(&counters->batches, (unsigned long long)n_reused);   // samples composited from a re-used network output
 	}
 	if (count_batches) {
 		__syncthreads();

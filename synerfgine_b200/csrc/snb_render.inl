@@ -118,7 +118,7 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	c->stage_begin(1);
 	int rc = SNB_OK;
 	AltCtl ctl; ctl.st = nullptr; ctl.target_queries = c->alt_target_queries; ctl.fixed_steps = 0; ctl.conditional = 0; ctl.external = c->alt_mode == 1;
-	ctl.lk = nullptr; ctl.park[0] = ctl.park[1] = nullptr; ctl.lists[0] = ctl.lists[1] = nullptr; ctl.phase = 0;
+	ctl.lk = nullptr; ctl.park[0] = ctl.park[1] = nullptr; ctl.lists[0] = ctl.lists[1] = nullptr; ctl.phase = 0; ctl.reuse_dup = c->dup_reuse ? 1u : 0u;
 	if (!alt) {
 		// Testbed::render_nerf hands camera_matrix1 to the compositor (src/testbed_nerf.cu:2761): depth is measured along the END-of-shutter camera
 		DevView mv = dv;

@@ -255,7 +255,7 @@ class Testbed:
     def counters(self):
         out = (C.c_uint64 * 4)()
         self._check(self.lib.snb_get_counters(self.ctx, out), "snb_get_counters")
-        return {"samples": out[0], "rays": out[1], "hits": out[2]}
+        return {"samples": out[0], "rays": out[1], "hits": out[2], "reused": out[3]}
 
     def march_stats(self):
         out = (C.c_uint64 * 4)()

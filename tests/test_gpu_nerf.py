@@ -126,7 +126,7 @@ def test_render_nerf_framebuffer(snb, orc, ctx, kind, alt, w, h, march):
     assert snb.snb_get_counters(ctx, cnt) == 0
     # network samples: the oracle (like the reference) evaluates whole 8-step batches and discards what follows a saturated
     # sample; the fused kernel composites step by step and never evaluates those, so it does the same or less work.
-    assert 0.85 * ns <= int(cnt[0]) <= ns + 8, (cnt[0], ns)   # counted: samples composited (both kernels)
+    assert 0.85 * ns <= int(cnt[0]) + int(cnt[3]) <= ns + 8, (cnt[0], cnt[3], ns)   # counted: samples composited = evaluated + composited from a re-used output (dup_reuse)
     if alt:
         pd = np.abs(pos.cpu().numpy() - rpos)
         assert (pd.max(-1) > 0.05).mean() < 2e-3
@@ -208,11 +208,18 @@ def test_full_size_properties(snb, ctx):
     b_fb, b_depth, b_pos, b_cnt = _render_full(snb, ctx, v)
     assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt   # counters = samples COMPOSITED ("ws" also evaluates, and ignores, the one or two in flight when a ray saturates)
     assert a_cnt[0] > 5_000_000 and (a_fb[..., 3] > 0.5).float().mean() > 0.05
+    # the other march kernels evaluate every sample through the network: compare them with the lane kernel doing the same (dup_reuse off)
+    assert snb.snb_set_option(ctx, b"dup_reuse", b"0") == 0
+    x_fb, x_depth, x_pos, x_cnt = _render_full(snb, ctx, v)
+    assert snb.snb_set_option(ctx, b"dup_reuse", b"1") == 0
+    over = int(((x_fb - a_fb).abs().amax(-1) > 1e-2).sum())
+    print(f"[dup_reuse at 1080p] network evaluations {a_cnt[0]} + {x_cnt[0] - a_cnt[0]} re-used; psnr {common.psnr(x_fb.cpu().numpy(), a_fb.cpu().numpy()):.1f} dB, pixels over 1e-2: {over}")
+    assert common.psnr(x_fb.cpu().numpy(), a_fb.cpu().numpy()) >= 50.0 and over <= 5e-4 * W * H
     for other in MARCHES[1:]:
         t_fb, t_depth, t_pos, t_cnt = _render_full(snb, ctx, v, march=other.encode())
-        err = (t_fb - a_fb).abs()
-        assert float(err.max()) <= 1e-2 and common.psnr(t_fb.cpu().numpy(), a_fb.cpu().numpy()) >= 50.0
-        assert abs(t_cnt[0] - a_cnt[0]) <= 1e-3 * a_cnt[0] and t_cnt[1] == a_cnt[1]     # a ray may saturate one sample earlier or later
+        err = (t_fb - x_fb).abs()
+        assert float(err.max()) <= 1e-2 and common.psnr(t_fb.cpu().numpy(), x_fb.cpu().numpy()) >= 50.0
+        assert abs(t_cnt[0] - x_cnt[0]) <= 1e-3 * x_cnt[0] and t_cnt[1] == x_cnt[1]     # a ray may saturate one sample earlier or later
     halo, total = tiles.halo_for(4), 0
     for r in range(4):
         s = tiles.strip_for(r, 4, W, halo)
@@ -270,6 +277,7 @@ def test_alt_schedule_matches_reference_wavefront(snb, orc, ctx, kind, w, h, tar
     d = set_model(snb, ctx, m)
     assert snb.snb_set_option(ctx, b"march", march.encode()) == 0
     assert snb.snb_set_option(ctx, b"alt_schedule", b"auto") == 0
+    assert snb.snb_set_option(ctx, b"dup_reuse", b"0") == 0                               # exact counts: every sample through the network, like the oracle
     assert snb.snb_set_option(ctx, b"alt_target_queries", str(target).encode()) == 0
     assert snb.snb_set_alt_schedule(ctx, None, 0) == 0                                   # cold start
     v = common.make_view(w, h)
@@ -306,6 +314,7 @@ def test_alt_schedule_matches_reference_wavefront(snb, orc, ctx, kind, w, h, tar
         assert np.abs(r8 - rfb).max() > 2e-2, "degenerate test: the schedule does not matter for this frame"
     finally:
         snb.snb_set_option(ctx, b"alt_schedule", b"auto"); snb.snb_set_option(ctx, b"alt_target_queries", b"2097152"); snb.snb_set_option(ctx, b"march", MARCHES[0].encode())
+        snb.snb_set_option(ctx, b"dup_reuse", b"1")
         snb.snb_set_alt_schedule(ctx, None, 0)
 
 
