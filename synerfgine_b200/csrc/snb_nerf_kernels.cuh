@@ -69,7 +69,7 @@ struct LockState {                     // device-resident, behind AltState
 	uint32_t sel;                      // which list / park buffer holds the checkpoint
 	uint32_t n_in, n_out;              // rays alive at the checkpoint / parked by the attempt in flight
 	uint32_t attempts, redos;          // statistics
-	unsigned long long pend_samples, pend_hits;   // counters of the attempt in flight (added to NerfCounters on commit)
+	unsigned long long pend_samples, pend_hits, pend_reused;   // counters of the attempt in flight (added to NerfCounters on commit)
 };
 struct AltCtl {
 	AltState* st;                     // nullptr: stock path / fixed batch length
@@ -142,10 +142,10 @@ __global__ void k_lock_begin(AltState* st, LockState* lk, uint32_t target, const
 	}
 	if (j == 0) {
 		lk->cur_batch = 0; lk->stop_batch = (uint32_t)kLockChunk; lk->sel = 0; lk->n_in = n; lk->n_out = 0; lk->attempts = 0; lk->redos = 0;
-		lk->pend_samples = 0ull; lk->pend_hits = 0ull;
+		lk->pend_samples = 0ull; lk->pend_hits = 0ull; lk->pend_reused = 0ull;
 		lk->done = (s0 >= 8u || n == 0u) ? 1u : 0u;
 		*queue_head = 0u; st->passes = 0; st->redo = 0; st->converged = 0;
-		if (counters) { counters->samples = 0; counters->rays = n; counters->hits = 0; }
+		if (counters) { counters->samples = 0; counters->rays = n; counters->hits = 0; counters->batches = 0; }
 	}
 }
 // After a prefix attempt over [b, stop): hist[j], b < j < stop, are the rays that started batch j in this attempt and n_out the rays
@@ -168,7 +168,7 @@ __global__ void k_lock_next(AltState* st, LockState* lk, uint32_t target, unsign
 		for (uint32_t j = stop + 1; j < (uint32_t)kAltSched; ++j) if (st->sched[j] < steps) st->sched[j] = (uint8_t)steps;   // guesses stay monotone
 		lk->cur_batch = stop; lk->sel ^= 1u; lk->n_in = n;
 		lk->stop_batch = stop + (uint32_t)kLockChunk < (uint32_t)kAltSched ? stop + (uint32_t)kLockChunk : (uint32_t)kAltSched;
-		if (counters) { counters->samples += lk->pend_samples; counters->hits += lk->pend_hits; }
+		if (counters) { counters->samples += lk->pend_samples; counters->hits += lk->pend_hits; counters->batches += lk->pend_reused; }
 		if (steps >= 8u || n == 0u || stop >= (uint32_t)kAltSched) lk->done = 1u;
 	} else {
 		// redo the chunk from the checkpoint with the corrected length (every entry before `bad` is exact now: progress is guaranteed)
@@ -176,7 +176,7 @@ __global__ void k_lock_next(AltState* st, LockState* lk, uint32_t target, unsign
 		for (uint32_t j = b + 1; j < (uint32_t)kAltSched; ++j) st->hist[j] = 0u;
 		lk->redos += 1;
 	}
-	lk->n_out = 0; lk->pend_samples = 0ull; lk->pend_hits = 0ull;
+	lk->n_out = 0; lk->pend_samples = 0ull; lk->pend_hits = 0ull; lk->pend_reused = 0ull;
 	*queue_head = 0u;
 }
 
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(256) k_alt_begin_pass(AltState* st, uint32_t f
                                                         NerfCounters* __restrict__ counters) {
 	if (!first_pass && !st->redo) return;
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i == 0) { *queue_head = 0u; if (first_pass) { st->passes = 0; st->redo = 0; st->converged = 0; } if (counters) { counters->samples = 0; counters->rays = 0; counters->hits = 0; } }
+	if (i == 0) { *queue_head = 0u; if (first_pass) { st->passes = 0; st->redo = 0; st->converged = 0; } if (counters) { counters->samples = 0; counters->rays = 0; counters->hits = 0; counters->batches = 0; } }
 	if (i < (uint32_t)kAltSched) st->hist[i] = 0u;
 	if (first_pass) return;
 	for (uint32_t p = i; p < n_px; p += gridDim.x * blockDim.x) {
@@ -650,7 +650,7 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		n_reused += __shfl_xor_sync(0xFFFFFFFFu, n_reused, s);
 	}
 	if (PH && alt.phase == 1) {   // a prefix attempt: its counts become final only when k_lock_next commits the chunk
-		if (lane == 0) { atomicAdd(&alt.lk->pend_samples, (unsigned long long)n_samples); atomicAdd(&alt.lk->pend_hits, (unsigned long long)n_hits); }
+		if (lane == 0) { atomicAdd(&alt.lk->pend_samples, (unsigned long long)n_samples); atomicAdd(&alt.lk->pend_hits, (unsigned long long)n_hits); if (n_reused) atomicAdd(&alt.lk->pend_reused, (unsigned long long)n_reused); }
 	} else if (lane == 0 && counters) {
 		atomicAdd(&counters->samples, (unsigned long long)n_samples);
 		atomicAdd(&counters->hits, (unsigned long long)n_hits);
