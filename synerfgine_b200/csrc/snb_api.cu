@@ -66,6 +66,8 @@ int snb_set_option(snb_ctx* c, const char* key, const char* value) {
 		c->alt_auto_lockstep = v != "0";
 	} else if (k == "dup_reuse") {
 		c->dup_reuse = v != "0";
+	} else if (k == "defer_srgb") {
+		c->defer_srgb = v != "0";
 	} else if (k == "alt_batch") {
 		const int b = atoi(v.c_str());
 		if (b < 1 || b > 8) return c->fail(SNB_ERR_ARG, "alt_batch: expected 1..8");
@@ -112,7 +114,7 @@ int snb_create(int device, void* cuda_stream, snb_ctx** out) {
 	c->device = device;
 	c->sm_count = prop.multiProcessorCount;
 	// SNB_<OPTION> in the environment sets the default of snb_set_option(ctx, "<option>", ...) (A/B runs without touching the caller)
-	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch", "alt_auto_lockstep", "dup_reuse", "bvh", "bvh_leaf"};
+	static const char* const kEnvOptions[] = {"march", "mlp", "overlap", "dead_terms", "lane_warps", "sng_block", "terms_block", "mesh_priority", "alt_schedule", "alt_batch", "alt_auto_lockstep", "dup_reuse", "defer_srgb", "bvh", "bvh_leaf"};
 	for (const char* opt : kEnvOptions) {
 		std::string env = std::string("SNB_") + opt;
 		for (char& ch : env) ch = (char)toupper((unsigned char)ch);

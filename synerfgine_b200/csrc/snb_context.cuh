@@ -79,6 +79,7 @@ struct snb_ctx {
 	int alt_mode = 0;
 	int alt_batch = 8;                 // batch length of alt_mode 2
 	bool dup_reuse = true;             // sng path: re-use the network output of the sample the compositor's rewind evaluates twice (option dup_reuse)
+	bool defer_srgb = true;            // sng path, lane kernel: the march stores sRGB colours, one pass over the tile converts them (option defer_srgb)
 	bool alt_auto_lockstep = true;     // alt_mode 0: frames whose camera or tile changed march the lock-step prefix (option alt_auto_lockstep); the march never reads the scene
 	float alt_last_cam[12] = {};       // camera and tile size of the last sng NeRF layer
 	int alt_last_tw = 0, alt_last_th = 0, alt_last_tx0 = 0, alt_last_ty0 = 0;

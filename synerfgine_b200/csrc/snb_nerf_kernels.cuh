@@ -35,6 +35,9 @@ struct NerfOut {                     // tile-sized output buffers
 	float* positions;                // xyz per pixel (alt path) or nullptr
 	// parity tap of the fused march (snb_set_sample_tap; all nullptr normally): per tile pixel the samples the kernel itself evaluates
 	float* tap_t; uint32_t* tap_cell; uint32_t* tap_n; uint32_t tap_cap;
+	// sng path, lane kernel: finished rays store the compositor's colour as it is and k_resolve_srgb converts the tile once the march is over
+	// (extract_from_payload's srgb_to_linear: three powf per ray, 12 KB of code, otherwise run by one or two lanes of a warp inside the march loop)
+	uint32_t raw_rgb;
 };
 
 // ---- batch schedule of the sng compositor ------------------------------------------------------------------------------------
@@ -358,6 +361,24 @@ __device__ __noinline__ void write_pixel(const DevView& view, const NerfOut& out
 	if (tmp.w > 0.2f) out.depth[l] = depth;
 	else if (rewrite) out.depth[l] = kMaxDepth;
 }
+// write_pixel of the sng path without the colour conversion (NerfOut::raw_rgb): the same stores, rgb left in sRGB for k_resolve_srgb.
+SNB_D void write_pixel_raw(const DevView& view, const NerfOut& out, uint32_t idx, v3 dir, float t, float4 rgba, float depth, bool rewrite) {
+	const int l = tile_local_index(view, idx);
+	const v3 orig_pos = view.cam.c3 + dir * t;
+	if (out.positions) { out.positions[l * 3 + 0] = orig_pos.x; out.positions[l * 3 + 1] = orig_pos.y; out.positions[l * 3 + 2] = orig_pos.z; }
+	out.fb[l] = rgba;
+	if (rgba.w > 0.2f) out.depth[l] = depth;
+	else if (rewrite) out.depth[l] = kMaxDepth;
+}
+// The conversion write_pixel_raw left out, over the whole tile: pixels no ray wrote hold 0, which srgb_to_linear maps to 0.
+__global__ void __launch_bounds__(256) k_resolve_srgb(float4* __restrict__ fb, uint32_t n_px) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_px) return;
+	float4 v = fb[i];
+	if (v.w == 0.0f) return;                                // never written (or cleared): rgb is 0 too
+	v.x = srgb_to_linear(v.x); v.y = srgb_to_linear(v.y); v.z = srgb_to_linear(v.z);
+	fb[i] = v;
+}
 __device__ __noinline__ void clear_pixel(const DevView& view, const NerfOut& out, uint32_t idx) {
 	const int l = tile_local_index(view, idx);
 	out.fb[l] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -477,7 +498,11 @@ k_nerf_march_fused(DevModel model, DevView view, NerfOut out, int render_mode, c
 		alive = false;
 		if (step_i + batch_steps >= kMarchIter) return;   // died in the last possible iteration: never compacted into the hit list
 		if (ALT) t = depth / dot(cam_fwd, d);             // payload.t rewrite at the end of composite_kernel_nerf_alt
-		if (rgba.w > 0.001f) { write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth, PH); ++n_hits; }
+		if (rgba.w > 0.001f) {
+			if (ALT && out.raw_rgb) write_pixel_raw(view, out, idx, d, t, rgba, depth, PH);
+			else write_pixel(view, out, ALT, render_mode, idx, d, t, rgba, depth, PH);
+			++n_hits;
+		}
 		else if (PH) clear_pixel(view, out, idx);   // an abandoned attempt may have written this pixel: back to the cleared state
 	};
 

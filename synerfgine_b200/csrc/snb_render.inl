@@ -105,6 +105,8 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	SNB_CUDA(c, cudaMemsetAsync(c->d_counters.p, 0, 2 * sizeof(NerfCounters), c->stream));   // counters + pipeline-balance cycles of the ws march
 	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
 	out.tap_t = nullptr; out.tap_cell = nullptr; out.tap_n = nullptr; out.tap_cap = 0;
+	// lane kernel on the sng path: colours stay in sRGB until k_resolve_srgb below (the Positions / Depth visualisations write other values: not deferred)
+	out.raw_rgb = (alt && c->march_variant == 3 && c->defer_srgb && render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH) ? 1u : 0u;
 	if (!alt && c->tap_t && c->march_variant == 3) { out.tap_t = c->tap_t; out.tap_cell = c->tap_cell; out.tap_n = c->tap_n; out.tap_cap = c->tap_cap; }
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches_x = (dv.tw + 7) / 8, patches_y = (dv.th + 3) / 4;
@@ -172,6 +174,10 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 			k_alt_verify<<<1, kAltSched, 0, c->stream>>>(st, c->alt_target_queries, qctl, (pass == passes - 1 || c->alt_mode == 1) ? 1u : 0u, c->alt_mode == 1 ? 1u : 0u);
 			SNB_LAUNCHED(c);
 		}
+	}
+	if (rc == SNB_OK && out.raw_rgb) {
+		k_resolve_srgb<<<(n_px + 255) / 256, 256, 0, c->stream>>>(out.fb, (uint32_t)n_px);
+		SNB_LAUNCHED(c);
 	}
 	c->stage_end(1);
 	return rc;
