@@ -173,6 +173,8 @@ const char* snb_version(void);
  *                    at a position that differs by the rounding of the rewind. 1: its network output is re-used (position, dt, depth and
  *                    termination are computed as always): a quarter fewer network evaluations on a 1080p frame, results within the
  *                    frame tolerance (>= 50 dB, counted pixels over 1e-2); 0: every sample goes through the network (exact counts)
+ *   "defer_srgb"   = "1" (default) | "0"   sng path, lane march: extract_from_payload's srgb_to_linear (src/testbed_nerf.cu:1614-1640) runs as one pass
+ *                    over the tile after the march (1) or per finished ray inside the march loop (0); bit-identical frames either way
  *   "alt_target_queries" = "2097152" target_n_queries of NerfTracer::trace_alt (src/testbed_nerf.cu:2188); tests lower it to exercise short batches on small frames
  * Implementation selectors (A/B measurements; frames are bit-identical unless noted):
  *   "march"      = "lane" (default: one ray per lane, MLPs on warp-level mma.sync) | "ws" (warp-specialised pipeline, MLPs on tcgen05 tensor

@@ -208,6 +208,12 @@ def test_full_size_properties(snb, ctx):
     b_fb, b_depth, b_pos, b_cnt = _render_full(snb, ctx, v)
     assert torch.equal(a_fb, b_fb) and torch.equal(a_depth, b_depth) and torch.equal(a_pos, b_pos) and a_cnt == b_cnt   # counters = samples COMPOSITED ("ws" also evaluates, and ignores, the one or two in flight when a ray saturates)
     assert a_cnt[0] > 5_000_000 and (a_fb[..., 3] > 0.5).float().mean() > 0.05
+    # the colour conversion of finished rays, inside the march loop (extract_from_payload's place) or as one pass over the tile afterwards
+    # (option defer_srgb, the default): the same function of the same value, so the frames are the same bits
+    assert snb.snb_set_option(ctx, b"defer_srgb", b"0") == 0
+    i_fb, i_depth, i_pos, i_cnt = _render_full(snb, ctx, v)
+    assert snb.snb_set_option(ctx, b"defer_srgb", b"1") == 0
+    assert torch.equal(i_fb, a_fb) and torch.equal(i_depth, a_depth) and torch.equal(i_pos, a_pos) and i_cnt == a_cnt
     # the other march kernels evaluate every sample through the network: compare them with the lane kernel doing the same (dup_reuse off)
     assert snb.snb_set_option(ctx, b"dup_reuse", b"0") == 0
     x_fb, x_depth, x_pos, x_cnt = _render_full(snb, ctx, v)
