@@ -106,7 +106,7 @@ static int render_nerf_layer(snb_ctx* c, const DevView& dv, bool alt, int render
 	NerfOut out; out.fb = reinterpret_cast<float4*>(fb); out.depth = depth; out.positions = positions;
 	out.tap_t = nullptr; out.tap_cell = nullptr; out.tap_n = nullptr; out.tap_cap = 0;
 	// lane kernel on the sng path: colours stay in sRGB until k_resolve_srgb below (the Positions / Depth visualisations write other values: not deferred)
-	out.raw_rgb = (alt && c->march_variant == 3 && c->defer_srgb && render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH) ? 1u : 0u;
+	out.raw_rgb = (alt && !dv.ex.enabled && c->march_variant == 3 && c->defer_srgb && render_mode != SNB_MODE_POSITIONS && render_mode != SNB_MODE_DEPTH) ? 1u : 0u;   // (an environment map pre-fills pixels the march never writes: stock path only today)
 	if (!alt && c->tap_t && c->march_variant == 3) { out.tap_t = c->tap_t; out.tap_cell = c->tap_cell; out.tap_n = c->tap_n; out.tap_cap = c->tap_cap; }
 	unsigned int* qctl = c->d_qctl.as<unsigned int>();
 	const int patches_x = (dv.tw + 7) / 8, patches_y = (dv.th + 3) / 4;
